@@ -1,0 +1,297 @@
+/*
+ * su2b200.h — C ABI of libsu2b200.so: the B200-native (sm_100a) implementation of SU2's
+ * implicit finite-volume flow iteration (edge residual/Jacobian assembly + preconditioned
+ * Krylov solve). This is the drop-in boundary: every entry point names the reference
+ * interface (su2code/SU2 v8.4.0, paths relative to the reference tree) it replaces.
+ *
+ * Conventions
+ *  - plain C types only; index arrays use `unsigned long` exactly like the reference
+ *    (CGeometry / CSysMatrix store `unsigned long`), converted to int32 on upload;
+ *  - every function returns 0 on success, non-zero on error; su2b200_last_error() gives
+ *    the message (the C++ shim turns it into SU2_MPI::Error, mpi_structure.hpp:111);
+ *  - the library owns all device memory behind the opaque handle; host pointers are read
+ *    or written during the call only;
+ *  - fp64 everywhere (su2double = double, code_config.hpp:128);
+ *  - one context == one MPI rank == one GPU; single caller thread per context.
+ *  - there is NO CPU fallback: every compute call runs CUDA kernels or fails.
+ */
+#ifndef SU2B200_H
+#define SU2B200_H
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef struct su2b200_ctx su2b200_ctx;
+
+/* ---- enums (values follow Common/include/option_structure.hpp where one exists) ---- */
+
+/* BC_TYPE, option_structure.hpp:1654-1688 */
+enum { SU2B200_EULER_WALL = 1, SU2B200_FAR_FIELD = 2, SU2B200_SYMMETRY_PLANE = 3,
+       SU2B200_HEAT_FLUX = 26, SU2B200_SEND_RECEIVE = 99 };
+
+/* convective scheme: CONV_NUM_METHOD_FLOW */
+enum { SU2B200_CONV_ROE = 0, SU2B200_CONV_JST = 1 };
+/* NUM_METHOD_GRAD / NUM_METHOD_GRAD_RECON */
+enum { SU2B200_GRAD_GREEN_GAUSS = 0, SU2B200_GRAD_LEAST_SQUARES = 1, SU2B200_GRAD_WEIGHTED_LEAST_SQUARES = 2 };
+/* SLOPE_LIMITER_FLOW */
+enum { SU2B200_LIMITER_NONE = 0, SU2B200_LIMITER_VENKATAKRISHNAN = 1, SU2B200_LIMITER_BARTH_JESPERSEN = 2 };
+/* LINEAR_SOLVER */
+enum { SU2B200_SOLVER_FGMRES = 0, SU2B200_SOLVER_BCGSTAB = 1, SU2B200_SOLVER_RESTARTED_FGMRES = 2 };
+/* LINEAR_SOLVER_PREC */
+enum { SU2B200_PREC_JACOBI = 0, SU2B200_PREC_LU_SGS = 1, SU2B200_PREC_ILU = 2 };
+/* which linear system of the context */
+enum { SU2B200_SYS_FLOW = 0, SU2B200_SYS_TURB = 1 };
+/* how the edge loop accumulates into points (both are atomics-free and deterministic):
+ * GATHER  = edge kernel stores fluxes + off-diagonal blocks, a point kernel sums them in
+ *           ascending edge order (the reference's "reducer strategy",
+ *           CFVMFlowSolverBase.inl:1575-1591 + CSysMatrix::SetDiagonalAsColumnSum);
+ * COLORED = one launch per edge colour with read-modify-write of residual/diagonal
+ *           (CFVMFlowSolverBase.inl:1543-1570 with CGeometry::GetEdgeColoring). */
+enum { SU2B200_ASSEMBLY_GATHER = 0, SU2B200_ASSEMBLY_COLORED = 1 };
+
+/* named device arrays that can be read back / overwritten (parity tests, restart, output) */
+enum {
+  SU2B200_ARR_SOLUTION = 0,      /* CVariable::Solution            [P][nVar]            */
+  SU2B200_ARR_SOLUTION_OLD = 1,  /* CVariable::Solution_Old        [P][nVar]            */
+  SU2B200_ARR_PRIMITIVE = 2,     /* CFlowVariable::Primitive       [P][nDim+9]          */
+  SU2B200_ARR_GRAD_RECON = 3,    /* Gradient_Reconstruction        [P][nDim+2][nDim]    */
+  SU2B200_ARR_GRAD_PRIM = 4,     /* Gradient_Primitive             [P][nDim+2][nDim]    */
+  SU2B200_ARR_LIMITER = 5,       /* Limiter_Primitive              [P][nDim+2]          */
+  SU2B200_ARR_DELTA_TIME = 6,    /* CVariable::Delta_Time          [P]                  */
+  SU2B200_ARR_LINSYSRES = 7,     /* CSolver::LinSysRes             [P][nVar]            */
+  SU2B200_ARR_LINSYSSOL = 8,     /* CSolver::LinSysSol             [P][nVar]            */
+  SU2B200_ARR_JACOBIAN = 9,      /* CSysMatrix::matrix             [nnz][nVar][nVar]    */
+  SU2B200_ARR_LAMBDA = 10,       /* CEulerVariable::Lambda         [P]                  */
+  SU2B200_ARR_SENSOR = 11,       /* CEulerVariable::Sensor         [P]                  */
+  SU2B200_ARR_UND_LAPL = 12,     /* CEulerVariable::Undivided_Laplacian [P][nVar]       */
+  SU2B200_ARR_MAX_LAMBDA_INV = 13,
+  SU2B200_ARR_MAX_LAMBDA_VISC = 14,
+  SU2B200_ARR_ILU = 15,          /* CSysMatrix::ILU_matrix         [nnz][nVar][nVar]    */
+  SU2B200_ARR_INVM = 16,         /* CSysMatrix::invM               [Pd][nVar][nVar]     */
+  SU2B200_ARR_UNDER_RELAX = 17,  /* CVariable::UnderRelaxation     [P]                  */
+  SU2B200_ARR_TURB_SOLUTION = 20,/* CTurbSAVariable::Solution      [P][1]               */
+  SU2B200_ARR_TURB_GRADIENT = 21,/* CScalarVariable::Gradient      [P][1][nDim]         */
+  SU2B200_ARR_TURB_LINSYSRES = 22,
+  SU2B200_ARR_TURB_LINSYSSOL = 23,
+  SU2B200_ARR_TURB_JACOBIAN = 24,
+  SU2B200_ARR_EDDY_VISC = 25,    /* CTurbVariable::muT             [P]                  */
+  SU2B200_ARR_VORTICITY = 26,    /* CFlowVariable::Vorticity       [P][3]               */
+  SU2B200_ARR_STRAIN_MAG = 27,   /* CFlowVariable::StrainMag       [P]                  */
+  SU2B200_ARR_WALL_DIST = 28,    /* CPoint::Wall_Distance          [P]                  */
+  SU2B200_ARR_TURB_DELTA_TIME = 29,
+  SU2B200_ARR_TURB_SOLUTION_OLD = 30
+};
+
+/* ---- lifecycle --------------------------------------------------------------------- */
+
+/* cudaSetDevice(device) + streams. Replaces the gpu_alloc calls in CSysMatrix::Initialize
+ * (Common/src/linear_algebra/CSysMatrix.cpp:142-160) and CSysVector::Initialize (CSysVector.cpp:55). */
+int su2b200_create(int device, su2b200_ctx** out);
+int su2b200_destroy(su2b200_ctx* ctx);
+/* message of the last failing call on this thread (GPUComms.cuh:46-53 gpuErrChk prints+exits instead) */
+const char* su2b200_last_error(void);
+int su2b200_version(void);
+int su2b200_synchronize(su2b200_ctx* ctx);
+
+/* ---- geometry: CGeometry dual grid + sparse pattern --------------------------------- */
+
+typedef struct {
+  int nDim;                          /* CGeometry::GetnDim()                                   */
+  unsigned long nPoint;              /* GetnPoint() (owned + halo)                             */
+  unsigned long nPointDomain;        /* GetnPointDomain()                                      */
+  unsigned long nEdge;               /* GetnEdge()                                             */
+  const unsigned long* edge_node0;   /* CEdge::Nodes column 0 [nEdge]  (CEdge.hpp:44, col-major)*/
+  const unsigned long* edge_node1;   /* CEdge::Nodes column 1 [nEdge]                          */
+  const double* edge_normal;         /* CEdge::Normal [nEdge][nDim] row-major (CEdge.hpp:46)   */
+  const double* coord;               /* CPoint::Coord [nPoint][nDim]  (CPoint.hpp)             */
+  const double* volume;              /* CPoint::Volume [nPoint]                                */
+  const unsigned long* point_ptr;    /* CPoint::Point outer ptr [nPoint+1] (neighbour CSR)     */
+  const unsigned long* point_nbr;    /* CPoint::Point inner idx [2*nEdge], reference order     */
+  const unsigned long* point_edge;   /* CPoint::Edge  inner idx [2*nEdge]                      */
+  const unsigned long* row_ptr;      /* CGeometry::GetSparsePattern outer ptr [nPoint+1] (CGeometry.cpp:3702) */
+  const unsigned long* col_ind;      /* inner idx [nnz], ascending, diagonal included          */
+  const unsigned long* dia_ptr;      /* diagonal position [nPoint]                             */
+  const unsigned long* edge_ptr;     /* GetEdgeToSparsePatternMap [nEdge][2] row-major (CGeometry.cpp:3720) */
+  const unsigned short* nNeighbor;   /* CPoint::nNeighbor [nPoint] (JST), may be NULL => from point_ptr */
+  const unsigned char* physical_boundary; /* CPoint::PhysicalBoundary [nPoint] (JST), may be NULL => derived from markers */
+  const double* wall_distance;       /* CPoint::Wall_Distance [nPoint], NULL unless RANS        */
+  const unsigned long* color_ptr;    /* GetEdgeColoring outer ptr [nColor+1], NULL => natural/own colouring */
+  const unsigned long* color_edges;  /* edge indices by colour [nEdge]                          */
+  unsigned long nColor;
+} su2b200_geometry_desc;
+
+/* Upload once after CSolver construction. */
+int su2b200_geometry_upload(su2b200_ctx* ctx, const su2b200_geometry_desc* g);
+
+/* One boundary marker: geometry->vertex[iMarker][iVertex]->{GetNode,GetNormal,GetNormal_Neighbor}
+ * and, for SYMMETRY_PLANE/EULER_WALL, the (possibly modified) unit normal of
+ * CGeometry::symmetryNormals (CGeometry.cpp:2469-2585); sym_unit_normal may be NULL => normal/|normal|.
+ * monitoring != 0 marks the marker as part of MARKER_MONITORING (force integration).
+ * heat_flux is MARKER_HEATFLUX's value / Heat_Flux_Ref (CNSSolver.cpp:440). */
+int su2b200_marker_upload(su2b200_ctx* ctx, int iMarker, int kindBC, unsigned long nVertex,
+                          const unsigned long* vertex_node, const double* vertex_normal,
+                          const unsigned long* vertex_normal_neighbor, const double* sym_unit_normal,
+                          int monitoring, double heat_flux);
+
+/* Halo tables of CGeometry::PreprocessP2PComms (CGeometry.cpp:139-332): neighbour ranks, cumulative
+ * point counts and the local point lists for send/recv. */
+int su2b200_p2p_upload(su2b200_ctx* ctx, int nNeighborRanks, const int* neighbor_rank,
+                       const int* nPoint_P2PSend /*[n+1] cumulative*/, const unsigned long* Local_Point_P2PSend,
+                       const int* nPoint_P2PRecv /*[n+1] cumulative*/, const unsigned long* Local_Point_P2PRecv);
+
+/* ---- configuration: the CConfig getters the hot path reads, as a POD ------------------ */
+
+typedef struct {
+  /* fluid (CIdealGas.cpp:40-52, CSutherland.hpp:47-56, CConstantPrandtl) -- non-dimensional values */
+  double gamma, gas_constant;
+  int viscous;                       /* NAVIER_STOKES / RANS                                  */
+  int rans_sa;                       /* KIND_TURB_MODEL= SA                                   */
+  int sa_negative;                   /* SA_OPTIONS= NEGATIVE                                  */
+  double mu_ref, mu_temperature_ref, mu_sutherland; /* Sutherland non-dim; mu_constant if mu_sutherland<0 */
+  double mu_constant;
+  double prandtl_lam, prandtl_turb;
+  /* free stream (CEulerSolver::GetDensity_Inf etc.) */
+  double density_inf, pressure_inf, velocity_inf[3], energy_inf, temperature_inf;
+  double nu_tilde_inf, eddy_visc_inf;
+  /* numerics */
+  int conv_scheme;                   /* CONV_NUM_METHOD_FLOW                                  */
+  int muscl;                         /* MUSCL_FLOW                                            */
+  double muscl_kappa;                /* MUSCL_KAPPA_FLOW (CConfig.cpp:2015)                   */
+  int limiter;                       /* SLOPE_LIMITER_FLOW                                    */
+  double venkat_coeff;               /* VENKAT_LIMITER_COEFF                                  */
+  double ref_elem_length;            /* REF_ELEM_LENGTH                                       */
+  int grad_method, grad_method_recon;/* NUM_METHOD_GRAD, NUM_METHOD_GRAD_RECON                */
+  double roe_kappa;                  /* ROE_KAPPA (0.5)                                       */
+  double entropy_fix;                /* ENTROPY_FIX_COEFF                                     */
+  double jst_kappa2, jst_kappa4;     /* JST_SENSOR_COEFF                                      */
+  double cent_jac_fix_factor;        /* CENTRAL_JACOBIAN_FIX_FACTOR                           */
+  /* time integration */
+  double cfl;                        /* CFL_NUMBER (LocalCFL of every point)                  */
+  double cfl_turb_ratio;             /* CFL_REDUCTION_TURB                                    */
+  double max_delta_time;             /* MAX_DELTA_TIME                                        */
+  double max_update_flow;            /* MAX_UPDATE_FLOW (0.2)                                 */
+  double max_update_sa;              /* MAX_UPDATE_SA (0.99)                                  */
+  /* linear solver */
+  int linear_solver, linear_prec;    /* LINEAR_SOLVER, LINEAR_SOLVER_PREC                     */
+  double linear_tol;                 /* LINEAR_SOLVER_ERROR                                   */
+  int linear_iter;                   /* LINEAR_SOLVER_ITER                                    */
+  int linear_restart;                /* LINEAR_SOLVER_RESTART_FREQUENCY                       */
+  int turb_linear_solver, turb_linear_prec, turb_linear_iter;
+  double turb_linear_tol;
+  /* forces (CFVMFlowSolverBase::Pressure_Forces) */
+  double aoa_deg, aos_deg, ref_area, ref_length, ref_origin[3];
+  /* implementation choices (not CConfig) */
+  int assembly;                      /* SU2B200_ASSEMBLY_*                                    */
+  int prec_partitions;               /* <=1: level-scheduled ILU0/LU-SGS == the reference's serial sweeps;
+                                        K>1: K nnz-balanced row partitions, block-Jacobi between them, exactly what the
+                                        reference does with LINEAR_SOLVER_PREC_THREADS=K (CSysMatrix.cpp:199-227,701-711) */
+} su2b200_flow_config;
+
+int su2b200_flow_configure(su2b200_ctx* ctx, const su2b200_flow_config* cfg);
+
+/* ---- state ---------------------------------------------------------------------------- */
+
+/* Allocates CVariable-equivalent device arrays and sets every point to the free stream
+ * (CEulerVariable ctor, CEulerSolver.cpp:293-297). Needs geometry + config. */
+int su2b200_flow_allocate(su2b200_ctx* ctx);
+/* element count of a named array (doubles) */
+long su2b200_array_size(su2b200_ctx* ctx, int which);
+int su2b200_array_download(su2b200_ctx* ctx, int which, double* host);
+int su2b200_array_upload(su2b200_ctx* ctx, int which, const double* host);
+/* NonPhysicalEdgeCounter (CFlowVariable.hpp:80-87), int8 per edge */
+int su2b200_edge_counter_download(su2b200_ctx* ctx, signed char* host);
+
+/* ---- CSolver virtuals of the flow solver (one call == one reference call) --------------- */
+
+/* CEulerSolver::Preprocessing (CEulerSolver.cpp:1667) / CNSSolver::Preprocessing (CNSSolver.cpp:70):
+ * primitives, [JST] lambda/sensor/laplacian, zero residual+Jacobian, [MUSCL] recon gradient + limiter,
+ * [viscous] primitive gradient, vorticity/strain. nonphysical = CEulerSolver::ErrorCounter. */
+int su2b200_flow_preprocessing(su2b200_ctx* ctx, int output, unsigned long* nonphysical_points);
+/* CSolver::Set_OldSolution */
+int su2b200_flow_set_old_solution(su2b200_ctx* ctx);
+/* CEulerSolver::SetTime_Step (CFVMFlowSolverBase.hpp:377-620) */
+int su2b200_flow_set_time_step(su2b200_ctx* ctx, double* min_dt, double* max_dt);
+/* CEulerSolver::Upwind_Residual / Centered_Residual -> EdgeFluxResidual (CFVMFlowSolverBase.inl:1517-1573)
+ * with the CNumericsSIMD functor chain (roe.hpp, centered.hpp, viscous_fluxes.hpp). */
+int su2b200_flow_edge_residual(su2b200_ctx* ctx, unsigned long* nonphysical_edges);
+/* CEulerSolver::BC_Far_Field (CEulerSolver.cpp:4780-5034) */
+int su2b200_flow_bc_far_field(su2b200_ctx* ctx, int iMarker);
+/* CFVMFlowSolverBase::BC_Sym_Plane == BC_Euler_Wall (CFVMFlowSolverBase.inl:1114-1272) */
+int su2b200_flow_bc_sym_plane(su2b200_ctx* ctx, int iMarker);
+/* CNSSolver::BC_HeatFlux_Wall (CNSSolver.cpp:423-578) */
+int su2b200_flow_bc_heatflux_wall(su2b200_ctx* ctx, int iMarker);
+/* CIntegration::Space_Integration (CIntegration.cpp:37-201): edge residual + all BCs in the reference's order */
+int su2b200_flow_space_integration(su2b200_ctx* ctx);
+/* CFVMFlowSolverBase::PrepareImplicitIteration_impl (CFVMFlowSolverBase.hpp:912-973);
+ * rms[nVar] = CSolver::Residual_RMS (sqrt(sum r^2 / N)), max[nVar], idx[nVar] = local point of the max */
+int su2b200_flow_prepare_implicit(su2b200_ctx* ctx, double* rms, double* max, unsigned long* idx);
+/* System.Solve(Jacobian, LinSysRes, LinSysSol) (CSysSolve.cpp:1318-1531, call site CFVMFlowSolverBase.inl:608) */
+int su2b200_flow_linear_solve(su2b200_ctx* ctx, unsigned long* iterations, double* residual);
+/* CFVMFlowSolverBase::CompleteImplicitIteration_impl (CFVMFlowSolverBase.hpp:983-1008) incl. under-relaxation */
+int su2b200_flow_complete_implicit(su2b200_ctx* ctx);
+/* CFVMFlowSolverBase::Pressure_Forces (+Friction_Forces) on MARKER_MONITORING: CL, CD, CSF, CMx..z, CFx..z */
+int su2b200_flow_forces(su2b200_ctx* ctx, double* coeffs /*[9]: CL CD CSF CFx CFy CFz CMx CMy CMz*/);
+
+/* ---- CTurbSASolver virtuals -------------------------------------------------------------- */
+int su2b200_turb_preprocessing(su2b200_ctx* ctx);        /* CTurbSASolver::Preprocessing (CTurbSASolver.cpp:176) */
+int su2b200_turb_set_time_step(su2b200_ctx* ctx);        /* CScalarSolver::SetTime_Step (CScalarSolver.inl:443) */
+int su2b200_turb_space_integration(su2b200_ctx* ctx);    /* Upwind_/Viscous_/Source_Residual + BCs */
+int su2b200_turb_prepare_implicit(su2b200_ctx* ctx, double* rms, double* max, unsigned long* idx);
+int su2b200_turb_linear_solve(su2b200_ctx* ctx, unsigned long* iterations, double* residual);
+int su2b200_turb_complete_implicit(su2b200_ctx* ctx);
+int su2b200_turb_postprocessing(su2b200_ctx* ctx);       /* CTurbSASolver::Postprocessing (mu_t) */
+
+/* ---- whole iterations (CMultiGridIntegration::MultiGrid_Iteration at MGLEVEL=0 +
+ *      CSingleGridIntegration::SingleGrid_Iteration(TURB_SOL)), state stays on the device --------- */
+typedef struct {
+  double rms_flow[5];          /* log10 not applied: CSolver::GetRes_RMS                       */
+  double rms_turb;
+  double CL, CD;
+  unsigned long linsol_iter_flow, linsol_iter_turb;
+  double linsol_res_flow, linsol_res_turb;
+  unsigned long nonphysical_points, nonphysical_edges;
+} su2b200_iter_report;
+int su2b200_iterate(su2b200_ctx* ctx, int nIter, su2b200_iter_report* reports /*[nIter], may be NULL*/);
+
+/* ---- CSysMatrix / CSysVector / CSysSolve level (host-buffer entry points, HtD/DtH inside) ---- */
+
+/* CSysMatrix::Initialize (CSysMatrix.cpp:86-247) for a system not tied to a flow state:
+ * creates system `which` of the context from a pattern. Geometry upload does this implicitly. */
+int su2b200_linsys_create(su2b200_ctx* ctx, int which, int nVar, unsigned long nPoint, unsigned long nPointDomain,
+                          const unsigned long* row_ptr, const unsigned long* col_ind);
+/* CSysMatrix::HtDTransfer (CSysMatrixGPU.cu:59-64) */
+int su2b200_linsys_set_matrix(su2b200_ctx* ctx, int which, const double* blocks);
+/* CSysMatrix::GPUMatrixVectorProduct (CSysMatrixGPU.cu:66-86) == MatrixVectorProduct (CSysMatrix.cpp:617-645):
+ * y = A x over owned rows; x,y host [nPoint][nVar]. */
+int su2b200_linsys_spmv(su2b200_ctx* ctx, int which, const double* x, double* y);
+/* CPreconditioner::Build() (CPreconditioner.hpp:49-75): BuildJacobiPreconditioner / BuildILUPreconditioner */
+int su2b200_linsys_build_preconditioner(su2b200_ctx* ctx, int which, int prec);
+/* CPreconditioner::operator()(u,v): ComputeJacobi/ILU/LU_SGSPreconditioner (CSysMatrix.cpp:660-888) */
+int su2b200_linsys_apply_preconditioner(su2b200_ctx* ctx, int which, int prec, const double* x, double* y);
+/* CSysSolve::Solve (CSysSolve.cpp:1318): b,x host [nPoint][nVar]; x0 = 0 */
+int su2b200_linsys_solve(su2b200_ctx* ctx, int which, int solver, int prec, double tol, int max_iter,
+                         const double* b, double* x, unsigned long* iterations, double* residual);
+/* CSysVector::dot (CSysVector.hpp:335-366) over owned entries, on the device */
+int su2b200_vector_dot(su2b200_ctx* ctx, int which, const double* a, const double* b, double* result);
+
+/* ---- communication: CSolver::InitiateComms/CompleteComms (CSolver.cpp:1406-1697) ------------ */
+/* 128-byte ncclUniqueId: rank 0 creates it, the host side broadcasts it (MPI_Bcast / torch.distributed) */
+int su2b200_comm_unique_id(unsigned char id[128]);
+int su2b200_comm_init(su2b200_ctx* ctx, int rank, int size, const unsigned char id[128]);
+/* halo exchange of a named array (MPI_QUANTITIES: SOLUTION, PRIMITIVE_GRADIENT, ...) */
+int su2b200_halo_exchange(su2b200_ctx* ctx, int which_array);
+
+/* ---- timing helpers used by bench.py (CUDA events on the context's compute stream) ----------- */
+int su2b200_timer_start(su2b200_ctx* ctx);
+int su2b200_timer_stop(su2b200_ctx* ctx, float* ms);
+/* kernels launched by this context since creation (bench.py's gpu_launches) */
+unsigned long su2b200_launch_count(su2b200_ctx* ctx);
+/* micro-benchmarks of the two roofline kernels on the resident state: average ms over `reps` launches */
+int su2b200_bench_edge_kernel(su2b200_ctx* ctx, int reps, float* ms_avg);
+int su2b200_bench_spmv(su2b200_ctx* ctx, int which, int reps, float* ms_avg);
+
+#ifdef __cplusplus
+}
+#endif
+#endif

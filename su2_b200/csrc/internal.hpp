@@ -1,0 +1,189 @@
+// Internal structures of libsu2b200 (not part of the C ABI).
+#pragma once
+#include <cuda_runtime.h>
+#include <cstdint>
+#include <cstdio>
+#include <cstring>
+#include <string>
+#include <vector>
+#include <stdexcept>
+#include "../../include/su2b200.h"
+
+namespace su2b200 {
+
+// ---- errors -------------------------------------------------------------------------------
+void set_error(const std::string& msg);
+struct Error : std::runtime_error { using std::runtime_error::runtime_error; };
+
+#define SU2B_CUDA(call)                                                                      \
+  do {                                                                                       \
+    cudaError_t e_ = (call);                                                                 \
+    if (e_ != cudaSuccess)                                                                   \
+      throw su2b200::Error(std::string(#call) + " failed: " + cudaGetErrorString(e_) + " at " + \
+                           __FILE__ + ":" + std::to_string(__LINE__));                       \
+  } while (0)
+
+#define SU2B_REQUIRE(cond, msg)                                      \
+  do {                                                               \
+    if (!(cond)) throw su2b200::Error(std::string(msg));             \
+  } while (0)
+
+// ---- device vector --------------------------------------------------------------------------
+template <class T>
+struct dvec {
+  T* p = nullptr;
+  size_t n = 0;
+  dvec() = default;
+  dvec(const dvec&) = delete;
+  dvec& operator=(const dvec&) = delete;
+  ~dvec() { release(); }
+  void release() {
+    if (p) cudaFree(p);
+    p = nullptr;
+    n = 0;
+  }
+  void alloc(size_t count) {
+    if (count == n && p) return;
+    release();
+    n = count;
+    if (count) SU2B_CUDA(cudaMalloc(&p, count * sizeof(T)));
+  }
+  void zero(cudaStream_t s = 0) {
+    if (n) SU2B_CUDA(cudaMemsetAsync(p, 0, n * sizeof(T), s));
+  }
+  void upload(const T* h, size_t count, cudaStream_t s = 0) {
+    alloc(count);
+    if (count) {
+      SU2B_CUDA(cudaMemcpyAsync(p, h, count * sizeof(T), cudaMemcpyHostToDevice, s));
+      SU2B_CUDA(cudaStreamSynchronize(s));
+    }
+  }
+  void upload(const std::vector<T>& h, cudaStream_t s = 0) { upload(h.data(), h.size(), s); }
+  void download(T* h, cudaStream_t s = 0) const {
+    if (n) {
+      SU2B_CUDA(cudaMemcpyAsync(h, p, n * sizeof(T), cudaMemcpyDeviceToHost, s));
+      SU2B_CUDA(cudaStreamSynchronize(s));
+    }
+  }
+  std::vector<T> to_host(cudaStream_t s = 0) const {
+    std::vector<T> h(n);
+    download(h.data(), s);
+    return h;
+  }
+};
+
+// ---- geometry ---------------------------------------------------------------------------------
+struct Marker {
+  int kind = 0;
+  int nVertex = 0;
+  int monitoring = 0;
+  double heat_flux = 0.0;
+  dvec<int> node;          // [nV]
+  dvec<double> normal;     // [nV][nDim]
+  dvec<int> normal_nbr;    // [nV]
+  dvec<double> unit_sym;   // [nV][nDim] unit normal used by symmetry/Euler-wall treatment
+  dvec<double> charac;     // [nV][nDim+9] CharacPrimVar (CFVMFlowSolverBase.hpp:176), zero-initialised
+};
+
+struct Geometry {
+  int nDim = 0;
+  int P = 0, Pd = 0, E = 0;
+  long nnz = 0;
+  dvec<int> edge_i, edge_j;       // [E]
+  dvec<double> edge_normal;       // SoA [nDim][E]
+  dvec<double> coord;             // [P][nDim]
+  dvec<double> volume;            // [P]
+  dvec<int> nbr_ptr, nbr_pt, nbr_edge;  // neighbour CSR in the reference's order
+  dvec<int> row_ptr, col_ind, dia_ptr;  // Jacobian pattern
+  dvec<int> edge_ij, edge_ji;     // [E] block index of (i,j) and (j,i)
+  dvec<int> gat_edge, gat_blk;    // per-point edge list sorted by edge index (see k_point_sum)
+  dvec<int> nnbr;                 // CPoint::nNeighbor
+  dvec<unsigned char> phys_bnd;   // CPoint::PhysicalBoundary
+  dvec<double> wall_dist;
+  // edge colouring (COLORED assembly)
+  std::vector<int> color_ptr;     // host
+  dvec<int> color_edges;
+  std::vector<Marker> markers;
+  bool uploaded = false;
+  bool have_phys_bnd = false;
+  // host copies needed by host-side setup (ILU level schedule)
+  std::vector<int> h_row_ptr, h_col_ind, h_dia_ptr;
+};
+
+// ---- block-CSR linear system (CSysMatrix + CSysVector + CSysSolve workspace) -----------------
+struct LinSys {
+  int nVar = 0;
+  int P = 0, Pd = 0;
+  long nnz = 0;
+  const int* row_ptr = nullptr;  // device, borrowed from Geometry or owned below
+  const int* col_ind = nullptr;
+  const int* dia_ptr = nullptr;
+  dvec<int> own_row_ptr, own_col_ind, own_dia_ptr;
+  std::vector<int> h_row_ptr, h_col_ind, h_dia_ptr;
+  dvec<double> A;      // [nnz][nVar*nVar]
+  dvec<double> ilu;    // ILU_matrix
+  dvec<double> invM;   // [Pd][nVar*nVar] inverse diagonal (Jacobi or ILU's U_ii^-1)
+  // level schedule for exact ILU0 build/apply (rows grouped by dependency level)
+  bool levels_ready = false;
+  std::vector<int> lvl_ptr_lower, lvl_ptr_upper;  // host offsets into the row lists
+  dvec<int> lvl_rows_lower, lvl_rows_upper;
+  int nlev_lower = 0, nlev_upper = 0;
+  // reference-style row partitions (block-Jacobi ILU across partitions); nparts <= 1: exact serial factor
+  int nparts = 1;
+  std::vector<int> h_parts;
+  dvec<int> parts;
+  // Krylov workspace
+  std::vector<dvec<double>*> work;   // lazily grown pool of [P*nVar] vectors
+  dvec<double> scalars;              // device scalars for reductions
+  double* h_scalars = nullptr;       // pinned host mirror
+  ~LinSys();
+  dvec<double>& vec(size_t i);
+  size_t vecLen() const { return (size_t)P * nVar; }
+};
+
+// ---- flow state ---------------------------------------------------------------------------------
+struct FlowState {
+  bool allocated = false;
+  int nVar = 0, nPrim = 0, nG = 0;
+  dvec<double> U, U_old, V;
+  dvec<double> grad_recon, grad_prim, limiter;
+  dvec<double> dt, lam_inv, lam_visc, under_relax;
+  dvec<double> lambda, sensor, und_lapl;     // JST
+  dvec<double> res, sol;                     // LinSysRes, LinSysSol
+  dvec<double> res_trunc;                    // Res_TruncError (zero without multigrid)
+  dvec<double> edge_flux;                    // SoA [nVar][E] (GATHER assembly)
+  dvec<signed char> edge_counter;            // NonPhysicalEdgeCounter
+  dvec<double> vorticity, strain_mag;
+  // turbulence (SA)
+  dvec<double> nu, nu_old, nu_grad, mu_t, turb_res, turb_sol, turb_dt, turb_under_relax, turb_edge_flux;
+  dvec<unsigned long long> counters;         // device counters (non-physical points/edges)
+  dvec<double> red;                          // reduction scratch
+  double* h_red = nullptr;                   // pinned
+  unsigned long long* h_counters = nullptr;  // pinned
+  bool recon_aliases_prim = false;           // Gradient_Reconstruction is Gradient_Primitive
+};
+
+}  // namespace su2b200
+
+struct su2b200_ctx {
+  int device = 0;
+  cudaStream_t stream = nullptr;
+  cudaStream_t comm_stream = nullptr;
+  cudaEvent_t ev0 = nullptr, ev1 = nullptr;
+  unsigned long launches = 0;
+  su2b200::Geometry geo;
+  su2b200_flow_config cfg{};
+  bool configured = false;
+  su2b200::FlowState fs;
+  su2b200::LinSys sys[2];
+  // comm
+  void* nccl = nullptr;
+  int rank = 0, nranks = 1;
+  std::vector<int> p2p_ranks, p2p_send_ptr, p2p_recv_ptr;
+  su2b200::dvec<int> p2p_send_idx, p2p_recv_idx;
+  su2b200::dvec<double> p2p_send_buf, p2p_recv_buf;
+  // last linear solve info
+  unsigned long lin_iters[2] = {0, 0};
+  double lin_res[2] = {0, 0};
+  double min_dt = 0, max_dt = 0;
+};

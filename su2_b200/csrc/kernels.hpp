@@ -1,0 +1,68 @@
+// Host-side launch wrappers (one per reference loop). All run on ctx->stream.
+#pragma once
+#include "internal.hpp"
+
+namespace su2b200 {
+
+// flow_kernels.cu
+void flow_primitives(su2b200_ctx* c);
+void flow_gradient(su2b200_ctx* c, int reconstruction, int nvars);
+void flow_limiter(su2b200_ctx* c);
+void flow_time_step(su2b200_ctx* c);
+void flow_jst_preprocess(su2b200_ctx* c);
+void flow_vorticity_strain(su2b200_ctx* c);
+void flow_prepare_implicit(su2b200_ctx* c, double* rms, double* mx, unsigned long* idx);
+void turb_prepare_implicit_generic(su2b200_ctx* c, double* rms, double* mx, unsigned long* idx);
+void flow_complete_implicit(su2b200_ctx* c);
+
+// edge_kernels.cu
+void flow_edge_residual(su2b200_ctx* c, unsigned long* nonphysical_edges);
+
+// bc_kernels.cu
+void flow_bc_far_field(su2b200_ctx* c, int iMarker);
+void flow_bc_sym_plane(su2b200_ctx* c, int iMarker);
+void flow_bc_heatflux_wall(su2b200_ctx* c, int iMarker);
+void flow_forces(su2b200_ctx* c, double* coeffs);
+
+// linalg.cu  (CSysMatrix / CSysVector)
+void linsys_bind_geometry(su2b200_ctx* c, int which, int nVar);
+void linsys_spmv(su2b200_ctx* c, LinSys& ls, const double* x, double* y);
+void linsys_build_jacobi(su2b200_ctx* c, LinSys& ls);
+void linsys_apply_jacobi(su2b200_ctx* c, LinSys& ls, const double* x, double* y);
+void linsys_build_ilu(su2b200_ctx* c, LinSys& ls);
+void linsys_apply_ilu(su2b200_ctx* c, LinSys& ls, const double* x, double* y);
+void linsys_apply_lusgs(su2b200_ctx* c, LinSys& ls, const double* x, double* y);
+void linsys_build_prec(su2b200_ctx* c, LinSys& ls, int prec);
+void linsys_apply_prec(su2b200_ctx* c, LinSys& ls, int prec, const double* x, double* y);
+double vec_dot(su2b200_ctx* c, LinSys& ls, const double* a, const double* b);
+void vec_axpy(su2b200_ctx* c, size_t n, double alpha, const double* x, double* y);           // y += alpha x
+void vec_axpby(su2b200_ctx* c, size_t n, double alpha, const double* x, double beta, double* y);  // y = alpha x + beta y
+void vec_scale(su2b200_ctx* c, size_t n, double alpha, double* x);
+void vec_copy(su2b200_ctx* c, size_t n, const double* x, double* y);
+void vec_set_scaled(su2b200_ctx* c, size_t n, double alpha, const double* x, double* y);     // y = alpha x
+
+// krylov.cu  (CSysSolve)
+unsigned long linsys_solve(su2b200_ctx* c, LinSys& ls, int solver, int prec, double tol, int max_iter,
+                           int restart, const double* b, double* x, double* residual);
+
+// turb_sa.cu
+void turb_preprocessing(su2b200_ctx* c);
+void turb_set_time_step(su2b200_ctx* c);
+void turb_space_integration(su2b200_ctx* c);
+void turb_complete_implicit(su2b200_ctx* c);
+void turb_postprocessing(su2b200_ctx* c);
+
+// comm.cu
+void halo_exchange(su2b200_ctx* c, double* arr, int count_per_point);
+double allreduce_sum(su2b200_ctx* c, double v);
+
+}  // namespace su2b200
+
+#define SU2B_LAUNCH(ctx, kern, grid, block, ...)                \
+  do {                                                          \
+    if ((grid) > 0) {                                           \
+      kern<<<(grid), (block), 0, (ctx)->stream>>>(__VA_ARGS__); \
+      (ctx)->launches++;                                        \
+      SU2B_CUDA(cudaGetLastError());                            \
+    }                                                           \
+  } while (0)

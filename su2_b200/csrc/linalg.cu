@@ -1,0 +1,298 @@
+// a16-a20, a23: block-CSR linear algebra on the device.
+//   CSysMatrix<T>::MatrixVectorProduct (Common/src/linear_algebra/CSysMatrix.cpp:617-645, RowProduct CSysMatrix.inl:173-181)
+//   Build/ComputeJacobiPreconditioner (:648-670), MatrixInverse (:548-601)
+//   Build/ComputeILUPreconditioner (:673-823), ComputeLU_SGSPreconditioner (:826-888)
+//   CSysVector<T> BLAS-1 (Common/include/linear_algebra/CSysVector.hpp:292-378)
+// Layout: blocks row-major [nnz][nVar][nVar] fp64 exactly like CSysMatrix::matrix; int32 row_ptr/col_ind/dia_ptr.
+//
+// Warp mapping used by every block kernel: LPB = nVar*nVar lanes own one scalar of a block (q = r*nVar+c),
+// BPW = 32/LPB blocks are processed per warp step. Block loads are therefore contiguous 8*LPB-byte reads.
+#include "internal.hpp"
+#include "kernels.hpp"
+#include <algorithm>
+
+namespace su2b200 {
+
+static inline int nblk(long n, int bs) { return (int)((n + bs - 1) / bs); }
+static constexpr unsigned FULL = 0xffffffffu;
+
+LinSys::~LinSys() {
+  for (auto* v : work) delete v;
+  if (h_scalars) cudaFreeHost(h_scalars);
+}
+dvec<double>& LinSys::vec(size_t i) {
+  while (work.size() <= i) work.push_back(new dvec<double>());
+  if (work[i]->n != vecLen()) {
+    work[i]->alloc(vecLen());
+    work[i]->zero();
+  }
+  return *work[i];
+}
+
+// ------------------------------------------------------------------------------------------------
+// BLAS-1
+// ------------------------------------------------------------------------------------------------
+__global__ void k_axpy(size_t n, double alpha, const double* __restrict__ x, double* __restrict__ y) {
+  for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (size_t)gridDim.x * blockDim.x)
+    y[i] += alpha * x[i];
+}
+__global__ void k_axpby(size_t n, double alpha, const double* __restrict__ x, double beta, double* __restrict__ y) {
+  for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (size_t)gridDim.x * blockDim.x)
+    y[i] = alpha * x[i] + beta * y[i];
+}
+__global__ void k_scale(size_t n, double alpha, double* __restrict__ x) {
+  for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (size_t)gridDim.x * blockDim.x)
+    x[i] *= alpha;
+}
+__global__ void k_set_scaled(size_t n, double alpha, const double* __restrict__ x, double* __restrict__ y) {
+  for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (size_t)gridDim.x * blockDim.x)
+    y[i] = alpha * x[i];
+}
+
+static inline int vec_grid(size_t n) { return (int)std::min<size_t>((n + 255) / 256, 148 * 8); }
+
+void vec_axpy(su2b200_ctx* c, size_t n, double alpha, const double* x, double* y) {
+  SU2B_LAUNCH(c, k_axpy, vec_grid(n), 256, n, alpha, x, y);
+}
+void vec_axpby(su2b200_ctx* c, size_t n, double alpha, const double* x, double beta, double* y) {
+  SU2B_LAUNCH(c, k_axpby, vec_grid(n), 256, n, alpha, x, beta, y);
+}
+void vec_scale(su2b200_ctx* c, size_t n, double alpha, double* x) { SU2B_LAUNCH(c, k_scale, vec_grid(n), 256, n, alpha, x); }
+void vec_set_scaled(su2b200_ctx* c, size_t n, double alpha, const double* x, double* y) {
+  SU2B_LAUNCH(c, k_set_scaled, vec_grid(n), 256, n, alpha, x, y);
+}
+void vec_copy(su2b200_ctx* c, size_t n, const double* x, double* y) {
+  SU2B_CUDA(cudaMemcpyAsync(y, x, n * sizeof(double), cudaMemcpyDeviceToDevice, c->stream));
+}
+
+// CSysVector::dot (CSysVector.hpp:335-366): sum over the owned (domain) entries, deterministic two-stage
+// reduction with warp shuffles; stage 2 is a single block so the result does not depend on scheduling.
+constexpr int DOT_BLOCKS = 148 * 4;
+__global__ void k_dot_stage1(size_t n, const double* __restrict__ a, const double* __restrict__ b,
+                             double* __restrict__ part) {
+  double s = 0.0;
+  for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (size_t)gridDim.x * blockDim.x)
+    s += a[i] * b[i];
+  __shared__ double sm[32];
+  for (int o = 16; o > 0; o >>= 1) s += __shfl_xor_sync(FULL, s, o);
+  const int w = threadIdx.x >> 5, l = threadIdx.x & 31;
+  if (l == 0) sm[w] = s;
+  __syncthreads();
+  if (w == 0) {
+    s = (l < (blockDim.x >> 5)) ? sm[l] : 0.0;
+    for (int o = 16; o > 0; o >>= 1) s += __shfl_xor_sync(FULL, s, o);
+    if (l == 0) part[blockIdx.x] = s;
+  }
+}
+__global__ void k_dot_stage2(int nb, const double* __restrict__ part, double* __restrict__ out) {
+  double s = 0.0;
+  for (int i = threadIdx.x; i < nb; i += blockDim.x) s += part[i];
+  __shared__ double sm[32];
+  for (int o = 16; o > 0; o >>= 1) s += __shfl_xor_sync(FULL, s, o);
+  const int w = threadIdx.x >> 5, l = threadIdx.x & 31;
+  if (l == 0) sm[w] = s;
+  __syncthreads();
+  if (w == 0) {
+    s = (l < (blockDim.x >> 5)) ? sm[l] : 0.0;
+    for (int o = 16; o > 0; o >>= 1) s += __shfl_xor_sync(FULL, s, o);
+    if (l == 0) out[0] = s;
+  }
+}
+
+static void ensure_scalars(LinSys& ls) {
+  if (ls.scalars.n < (size_t)DOT_BLOCKS + 64) ls.scalars.alloc(DOT_BLOCKS + 64);
+  if (!ls.h_scalars) SU2B_CUDA(cudaMallocHost(&ls.h_scalars, 64 * sizeof(double)));
+}
+
+double vec_dot(su2b200_ctx* c, LinSys& ls, const double* a, const double* b) {
+  ensure_scalars(ls);
+  const size_t n = (size_t)ls.Pd * ls.nVar;
+  const int nb = (int)std::min<size_t>((n + 255) / 256, DOT_BLOCKS);
+  SU2B_LAUNCH(c, k_dot_stage1, nb, 256, n, a, b, ls.scalars.p);
+  SU2B_LAUNCH(c, k_dot_stage2, 1, 256, nb, ls.scalars.p, ls.scalars.p + DOT_BLOCKS);
+  SU2B_CUDA(cudaMemcpyAsync(ls.h_scalars, ls.scalars.p + DOT_BLOCKS, sizeof(double), cudaMemcpyDeviceToHost, c->stream));
+  SU2B_CUDA(cudaStreamSynchronize(c->stream));
+  double v = ls.h_scalars[0];
+  if (c->nranks > 1) v = allreduce_sum(c, v);
+  return v;
+}
+
+// ------------------------------------------------------------------------------------------------
+// SpMV: one warp per block-row.
+// ------------------------------------------------------------------------------------------------
+template <int NV>
+__global__ void __launch_bounds__(256) k_spmv(int Pd, const int* __restrict__ row_ptr, const int* __restrict__ col_ind,
+                                              const double* __restrict__ A, const double* __restrict__ x,
+                                              double* __restrict__ y) {
+  constexpr int LPB = NV * NV;
+  constexpr int BPW = 32 / LPB;
+  const int warp = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+  const int lane = threadIdx.x & 31;
+  if (warp >= Pd) return;
+  const int g = lane / LPB, q = lane % LPB, cc = q % NV;
+  const bool active = g < BPW;
+  const int kb = row_ptr[warp], ke = row_ptr[warp + 1];
+  double acc = 0.0;
+  if (active) {
+    for (int k = kb + g; k < ke; k += BPW) {
+      const int col = col_ind[k];
+      acc += A[(size_t)k * LPB + q] * x[(size_t)col * NV + cc];
+    }
+  }
+  // reduce over the column index within a block row (lanes q = r*NV .. r*NV+NV-1 are adjacent)
+  double s = acc;
+#pragma unroll
+  for (int o = 1; o < NV; ++o) {
+    const double t = __shfl_down_sync(FULL, acc, o);
+    s += t;
+  }
+  // s is valid on lanes with cc == 0; now add the BPW sub-groups
+#pragma unroll
+  for (int gg = 1; gg < BPW; ++gg) {
+    const double t = __shfl_down_sync(FULL, s, gg * LPB);
+    if (g == 0) s += t;
+  }
+  if (active && g == 0 && cc == 0) y[(size_t)warp * NV + q / NV] = s;
+}
+
+// scalar CSR (nVar == 1): 8 lanes per row
+__global__ void __launch_bounds__(256) k_spmv_scalar(int Pd, const int* __restrict__ row_ptr,
+                                                     const int* __restrict__ col_ind, const double* __restrict__ A,
+                                                     const double* __restrict__ x, double* __restrict__ y) {
+  const int t = blockIdx.x * blockDim.x + threadIdx.x;
+  const int row = t >> 3, l = t & 7;
+  double acc = 0.0;
+  if (row < Pd) {
+    for (int k = row_ptr[row] + l; k < row_ptr[row + 1]; k += 8) acc += A[k] * x[col_ind[k]];
+  }
+  acc += __shfl_down_sync(FULL, acc, 4, 8);
+  acc += __shfl_down_sync(FULL, acc, 2, 8);
+  acc += __shfl_down_sync(FULL, acc, 1, 8);
+  if (row < Pd && l == 0) y[row] = acc;
+}
+
+void linsys_spmv(su2b200_ctx* c, LinSys& ls, const double* x, double* y) {
+  const long threads = (long)ls.Pd * 32;
+  switch (ls.nVar) {
+    case 1: SU2B_LAUNCH(c, k_spmv_scalar, nblk((long)ls.Pd * 8, 256), 256, ls.Pd, ls.row_ptr, ls.col_ind, ls.A.p, x, y); break;
+    case 4: SU2B_LAUNCH(c, k_spmv<4>, nblk(threads, 256), 256, ls.Pd, ls.row_ptr, ls.col_ind, ls.A.p, x, y); break;
+    case 5: SU2B_LAUNCH(c, k_spmv<5>, nblk(threads, 256), 256, ls.Pd, ls.row_ptr, ls.col_ind, ls.A.p, x, y); break;
+    default: throw Error("linsys_spmv: unsupported nVar");
+  }
+  if (c->nranks > 1) halo_exchange(c, y, ls.nVar);
+}
+
+// ------------------------------------------------------------------------------------------------
+// Dense nVar x nVar helpers (per thread, registers/local memory)
+// ------------------------------------------------------------------------------------------------
+__device__ __forceinline__ void regularize_pivot(double& pivot) {
+  const double eps = (double)1e-12f;  // `const float eps = 1e-12` in RegularizePivot (CSysMatrix.cpp:500-508)
+  if (fabs(pivot) < eps) pivot = copysign(eps, pivot);
+}
+
+// CSysMatrix::MatrixInverse (CSysMatrix.cpp:548-601); A is destroyed.
+template <int NV>
+__device__ __forceinline__ void matrix_inverse(double* A, double* M) {
+#pragma unroll
+  for (int i = 0; i < NV; ++i)
+#pragma unroll
+    for (int j = 0; j < NV; ++j) M[i * NV + j] = (i == j) ? 1.0 : 0.0;
+#pragma unroll
+  for (int i = 1; i < NV; ++i) {
+#pragma unroll
+    for (int j = 0; j < i; ++j) {
+      regularize_pivot(A[j * NV + j]);
+      const double w = A[i * NV + j] / A[j * NV + j];
+#pragma unroll
+      for (int k = j; k < NV; ++k) A[i * NV + k] -= w * A[j * NV + k];
+#pragma unroll
+      for (int k = 0; k <= j; ++k) M[i * NV + k] -= w * M[j * NV + k];
+    }
+  }
+#pragma unroll
+  for (int i = NV - 1; i >= 0; --i) {
+#pragma unroll
+    for (int j = i + 1; j < NV; ++j)
+#pragma unroll
+      for (int k = 0; k < NV; ++k) M[i * NV + k] -= A[i * NV + j] * M[j * NV + k];
+    regularize_pivot(A[i * NV + i]);
+#pragma unroll
+    for (int k = 0; k < NV; ++k) M[i * NV + k] /= A[i * NV + i];
+  }
+}
+
+// CSysMatrix::Gauss_Elimination (CSysMatrix.cpp:510-545); A and v are modified, v holds the solution.
+template <int NV>
+__device__ __forceinline__ void gauss_elimination(double* A, double* v) {
+#pragma unroll
+  for (int i = 1; i < NV; ++i) {
+#pragma unroll
+    for (int j = 0; j < i; ++j) {
+      regularize_pivot(A[j * NV + j]);
+      const double w = A[i * NV + j] / A[j * NV + j];
+#pragma unroll
+      for (int k = j; k < NV; ++k) A[i * NV + k] -= w * A[j * NV + k];
+      v[i] -= w * v[j];
+    }
+  }
+#pragma unroll
+  for (int i = NV - 1; i >= 0; --i) {
+#pragma unroll
+    for (int j = i + 1; j < NV; ++j) v[i] -= A[i * NV + j] * v[j];
+    regularize_pivot(A[i * NV + i]);
+    v[i] /= A[i * NV + i];
+  }
+}
+
+// ------------------------------------------------------------------------------------------------
+// Jacobi
+// ------------------------------------------------------------------------------------------------
+template <int NV>
+__global__ void k_jacobi_build(int Pd, const int* __restrict__ dia_ptr, const double* __restrict__ A,
+                               double* __restrict__ invM) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= Pd) return;
+  double B[NV * NV], M[NV * NV];
+  const double* D = A + (size_t)dia_ptr[i] * NV * NV;
+#pragma unroll
+  for (int k = 0; k < NV * NV; ++k) B[k] = D[k];
+  matrix_inverse<NV>(B, M);
+#pragma unroll
+  for (int k = 0; k < NV * NV; ++k) invM[(size_t)i * NV * NV + k] = M[k];
+}
+
+template <int NV>
+__global__ void k_jacobi_apply(int Pd, const double* __restrict__ invM, const double* __restrict__ x,
+                               double* __restrict__ y) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= Pd) return;
+  double v[NV];
+#pragma unroll
+  for (int k = 0; k < NV; ++k) v[k] = x[(size_t)i * NV + k];
+#pragma unroll
+  for (int r = 0; r < NV; ++r) {
+    double s = 0.0;
+#pragma unroll
+    for (int k = 0; k < NV; ++k) s += invM[(size_t)i * NV * NV + r * NV + k] * v[k];
+    y[(size_t)i * NV + r] = s;
+  }
+}
+
+void linsys_build_jacobi(su2b200_ctx* c, LinSys& ls) {
+  ls.invM.alloc((size_t)ls.Pd * ls.nVar * ls.nVar);
+  switch (ls.nVar) {
+    case 1: SU2B_LAUNCH(c, k_jacobi_build<1>, nblk(ls.Pd, 128), 128, ls.Pd, ls.dia_ptr, ls.A.p, ls.invM.p); break;
+    case 4: SU2B_LAUNCH(c, k_jacobi_build<4>, nblk(ls.Pd, 128), 128, ls.Pd, ls.dia_ptr, ls.A.p, ls.invM.p); break;
+    case 5: SU2B_LAUNCH(c, k_jacobi_build<5>, nblk(ls.Pd, 128), 128, ls.Pd, ls.dia_ptr, ls.A.p, ls.invM.p); break;
+    default: throw Error("jacobi: unsupported nVar");
+  }
+}
+void linsys_apply_jacobi(su2b200_ctx* c, LinSys& ls, const double* x, double* y) {
+  switch (ls.nVar) {
+    case 1: SU2B_LAUNCH(c, k_jacobi_apply<1>, nblk(ls.Pd, 128), 128, ls.Pd, ls.invM.p, x, y); break;
+    case 4: SU2B_LAUNCH(c, k_jacobi_apply<4>, nblk(ls.Pd, 128), 128, ls.Pd, ls.invM.p, x, y); break;
+    case 5: SU2B_LAUNCH(c, k_jacobi_apply<5>, nblk(ls.Pd, 128), 128, ls.Pd, ls.invM.p, x, y); break;
+    default: throw Error("jacobi: unsupported nVar");
+  }
+  if (c->nranks > 1) halo_exchange(c, y, ls.nVar);
+}

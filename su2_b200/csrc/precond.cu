@@ -1,0 +1,473 @@
+// a17-a19: ILU(0) and LU-SGS on the device.
+//   CSysMatrix<T>::BuildILUPreconditioner   (Common/src/linear_algebra/CSysMatrix.cpp:673-767)
+//   CSysMatrix<T>::ComputeILUPreconditioner (:770-823)
+//   CSysMatrix<T>::ComputeLU_SGSPreconditioner (:826-888), Lower/Upper/DiagonalProduct (CSysMatrix.inl:184-211)
+//
+// The reference factorises the owned sub-matrix [0, nPointDomain) per MPI rank and, with OpenMP, per
+// nnz-balanced row partition [begin, end) (block-Jacobi between partitions, CSysMatrix.cpp:199-227, :701-711).
+// Two schedules are provided for the same arithmetic:
+//   exact (ilu_exact=1): one partition == the serial reference; rows are grouped by dependency level
+//                        (level-scheduled triangular sweeps), one warp per row, one launch per level;
+//   partitioned        : K partitions as the reference does with K threads; one warp walks one partition
+//                        sequentially, all partitions in one launch.
+// In both, a warp owns a row: lane q = r*nVar + c holds one scalar of a block, products use shuffles.
+#include "internal.hpp"
+#include "kernels.hpp"
+#include <algorithm>
+
+namespace su2b200 {
+
+static inline int nblk(long n, int bs) { return (int)((n + bs - 1) / bs); }
+static constexpr unsigned FULL = 0xffffffffu;
+
+template <int NV>
+__device__ __forceinline__ void matrix_inverse_d(double* A, double* M);  // defined below (copy of linalg.cu's)
+
+__device__ __forceinline__ void reg_pivot(double& pivot) {
+  const double eps = (double)1e-12f;
+  if (fabs(pivot) < eps) pivot = copysign(eps, pivot);
+}
+template <int NV>
+__device__ __forceinline__ void matrix_inverse_d(double* A, double* M) {
+#pragma unroll
+  for (int i = 0; i < NV; ++i)
+#pragma unroll
+    for (int j = 0; j < NV; ++j) M[i * NV + j] = (i == j) ? 1.0 : 0.0;
+#pragma unroll
+  for (int i = 1; i < NV; ++i) {
+#pragma unroll
+    for (int j = 0; j < i; ++j) {
+      reg_pivot(A[j * NV + j]);
+      const double w = A[i * NV + j] / A[j * NV + j];
+#pragma unroll
+      for (int k = j; k < NV; ++k) A[i * NV + k] -= w * A[j * NV + k];
+#pragma unroll
+      for (int k = 0; k <= j; ++k) M[i * NV + k] -= w * M[j * NV + k];
+    }
+  }
+#pragma unroll
+  for (int i = NV - 1; i >= 0; --i) {
+#pragma unroll
+    for (int j = i + 1; j < NV; ++j)
+#pragma unroll
+      for (int k = 0; k < NV; ++k) M[i * NV + k] -= A[i * NV + j] * M[j * NV + k];
+    reg_pivot(A[i * NV + i]);
+#pragma unroll
+    for (int k = 0; k < NV; ++k) M[i * NV + k] /= A[i * NV + i];
+  }
+}
+template <int NV>
+__device__ __forceinline__ void gauss_elim_d(double* A, double* v) {
+#pragma unroll
+  for (int i = 1; i < NV; ++i) {
+#pragma unroll
+    for (int j = 0; j < i; ++j) {
+      reg_pivot(A[j * NV + j]);
+      const double w = A[i * NV + j] / A[j * NV + j];
+#pragma unroll
+      for (int k = j; k < NV; ++k) A[i * NV + k] -= w * A[j * NV + k];
+      v[i] -= w * v[j];
+    }
+  }
+#pragma unroll
+  for (int i = NV - 1; i >= 0; --i) {
+#pragma unroll
+    for (int j = i + 1; j < NV; ++j) v[i] -= A[i * NV + j] * v[j];
+    reg_pivot(A[i * NV + i]);
+    v[i] /= A[i * NV + i];
+  }
+}
+
+// C[q] = sum_m A[r][m] * B[m][c] with A,B distributed one scalar per lane (lanes 0..NV*NV-1)
+template <int NV>
+__device__ __forceinline__ double warp_matmul(double a, double b, int r, int cc) {
+  double s = 0.0;
+#pragma unroll
+  for (int m = 0; m < NV; ++m) {
+    const double am = __shfl_sync(FULL, a, r * NV + m);
+    const double bm = __shfl_sync(FULL, b, m * NV + cc);
+    s += am * bm;
+  }
+  return s;
+}
+
+// ---- one ILU(0) row, warp-cooperative (IKJ variant, CSysMatrix.cpp:714-760) -----------------------
+template <int NV>
+__device__ __forceinline__ void ilu_factor_row(int i, int begin, int end, const int* __restrict__ row_ptr,
+                                               const int* __restrict__ col_ind, const int* __restrict__ dia_ptr,
+                                               double* __restrict__ ILU, double* __restrict__ invM, int lane) {
+  constexpr int LPB = NV * NV;
+  const int q = lane < LPB ? lane : LPB - 1;  // idle lanes mirror the last scalar (never store)
+  const bool act = lane < LPB;
+  const int r = q / NV, cc = q % NV;
+  const int rb = row_ptr[i], re = row_ptr[i + 1], di = dia_ptr[i];
+  for (int idx = rb; idx < di; ++idx) {
+    const int j = col_ind[idx];
+    if (j < begin) continue;
+    const double aij = ILU[(size_t)idx * LPB + q];
+    const double inv = invM[(size_t)j * LPB + q];
+    const double w = warp_matmul<NV>(aij, inv, r, cc);  // weight = A_ij * inv(A_jj)
+    for (int idx2 = dia_ptr[j] + 1; idx2 < row_ptr[j + 1]; ++idx2) {
+      const int k = col_ind[idx2];
+      if (k >= end) break;
+      // find (i,k) in row i
+      int pos = -1;
+      for (int s = rb; s < re; ++s)
+        if (col_ind[s] == k) { pos = s; break; }
+      if (pos < 0) continue;
+      const double ajk = ILU[(size_t)idx2 * LPB + q];
+      const double aux = warp_matmul<NV>(w, ajk, r, cc);
+      if (act) ILU[(size_t)pos * LPB + q] -= aux;
+    }
+    if (act) ILU[(size_t)idx * LPB + q] = w;
+    __syncwarp();
+  }
+  // invM_i = inverse of the (updated) diagonal block; every lane inverts redundantly, lane q stores entry q
+  double B[NV * NV], M[NV * NV];
+#pragma unroll
+  for (int k = 0; k < NV * NV; ++k) B[k] = ILU[(size_t)di * LPB + k];
+  matrix_inverse_d<NV>(B, M);
+  if (act) invM[(size_t)i * LPB + q] = M[q];
+}
+
+// ---- forward / backward substitution rows (CSysMatrix.cpp:791-817) ------------------------------------
+template <int NV>
+__device__ __forceinline__ void ilu_forward_row(int i, int begin, const int* __restrict__ row_ptr,
+                                                const int* __restrict__ col_ind, const int* __restrict__ dia_ptr,
+                                                const double* __restrict__ ILU, double* __restrict__ y, int lane) {
+  constexpr int LPB = NV * NV;
+  const int q = lane < LPB ? lane : LPB - 1;
+  const int cc = q % NV;
+  double acc = 0.0;
+  for (int idx = row_ptr[i]; idx < dia_ptr[i]; ++idx) {
+    const int j = col_ind[idx];
+    if (j < begin) continue;
+    acc += ILU[(size_t)idx * LPB + q] * y[(size_t)j * NV + cc];
+  }
+  double s = acc;
+#pragma unroll
+  for (int o = 1; o < NV; ++o) s += __shfl_down_sync(FULL, acc, o);
+  if (lane < LPB && cc == 0) y[(size_t)i * NV + q / NV] -= s;
+}
+
+template <int NV>
+__device__ __forceinline__ void ilu_backward_row(int i, int end, const int* __restrict__ row_ptr,
+                                                 const int* __restrict__ col_ind, const int* __restrict__ dia_ptr,
+                                                 const double* __restrict__ ILU, const double* __restrict__ invM,
+                                                 double* __restrict__ y, int lane) {
+  constexpr int LPB = NV * NV;
+  const int q = lane < LPB ? lane : LPB - 1;
+  const int r = q / NV, cc = q % NV;
+  double acc = 0.0;
+  for (int idx = dia_ptr[i] + 1; idx < row_ptr[i + 1]; ++idx) {
+    const int j = col_ind[idx];
+    if (j >= end) break;
+    acc += ILU[(size_t)idx * LPB + q] * y[(size_t)j * NV + cc];
+  }
+  double s = acc;
+#pragma unroll
+  for (int o = 1; o < NV; ++o) s += __shfl_down_sync(FULL, acc, o);
+  // aux[r] = y_i[r] - s (valid on lanes with cc == 0, i.e. lane r*NV)
+  const double aux_r = y[(size_t)i * NV + r] - s;
+  // x_i = invM_i * aux : lane q needs aux[cc], held by lane cc*NV
+  const double aux_c = __shfl_sync(FULL, aux_r, cc * NV);
+  const double prod = invM[(size_t)i * LPB + q] * aux_c;
+  double t = prod;
+#pragma unroll
+  for (int o = 1; o < NV; ++o) t += __shfl_down_sync(FULL, prod, o);
+  __syncwarp();
+  if (lane < LPB && cc == 0) y[(size_t)i * NV + r] = t;
+}
+
+// ---- level-scheduled kernels: one warp per row of the level ----------------------------------------------
+template <int NV>
+__global__ void k_ilu_factor_level(int n, const int* __restrict__ rows, int begin, int end,
+                                   const int* __restrict__ row_ptr, const int* __restrict__ col_ind,
+                                   const int* __restrict__ dia_ptr, double* __restrict__ ILU, double* __restrict__ invM) {
+  const int w = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+  if (w >= n) return;
+  ilu_factor_row<NV>(rows[w], begin, end, row_ptr, col_ind, dia_ptr, ILU, invM, threadIdx.x & 31);
+}
+template <int NV>
+__global__ void k_ilu_forward_level(int n, const int* __restrict__ rows, int begin, const int* __restrict__ row_ptr,
+                                    const int* __restrict__ col_ind, const int* __restrict__ dia_ptr,
+                                    const double* __restrict__ ILU, double* __restrict__ y) {
+  const int w = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+  if (w >= n) return;
+  ilu_forward_row<NV>(rows[w], begin, row_ptr, col_ind, dia_ptr, ILU, y, threadIdx.x & 31);
+}
+template <int NV>
+__global__ void k_ilu_backward_level(int n, const int* __restrict__ rows, int end, const int* __restrict__ row_ptr,
+                                     const int* __restrict__ col_ind, const int* __restrict__ dia_ptr,
+                                     const double* __restrict__ ILU, const double* __restrict__ invM,
+                                     double* __restrict__ y) {
+  const int w = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+  if (w >= n) return;
+  ilu_backward_row<NV>(rows[w], end, row_ptr, col_ind, dia_ptr, ILU, invM, y, threadIdx.x & 31);
+}
+
+// ---- partitioned kernels: one warp per partition, rows in sequence ---------------------------------------
+template <int NV>
+__global__ void k_ilu_factor_part(int nparts, const int* __restrict__ part, const int* __restrict__ row_ptr,
+                                  const int* __restrict__ col_ind, const int* __restrict__ dia_ptr,
+                                  double* __restrict__ ILU, double* __restrict__ invM) {
+  const int w = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+  if (w >= nparts) return;
+  const int begin = part[w], end = part[w + 1];
+  for (int i = begin; i < end; ++i) {
+    ilu_factor_row<NV>(i, begin, end, row_ptr, col_ind, dia_ptr, ILU, invM, threadIdx.x & 31);
+    __syncwarp();
+  }
+}
+template <int NV>
+__global__ void k_ilu_apply_part(int nparts, const int* __restrict__ part, const int* __restrict__ row_ptr,
+                                 const int* __restrict__ col_ind, const int* __restrict__ dia_ptr,
+                                 const double* __restrict__ ILU, const double* __restrict__ invM,
+                                 double* __restrict__ y) {
+  const int w = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+  if (w >= nparts) return;
+  const int begin = part[w], end = part[w + 1];
+  const int lane = threadIdx.x & 31;
+  for (int i = begin + 1; i < end; ++i) {
+    ilu_forward_row<NV>(i, begin, row_ptr, col_ind, dia_ptr, ILU, y, lane);
+    __syncwarp();
+  }
+  for (int i = end - 1; i >= begin; --i) {
+    ilu_backward_row<NV>(i, end, row_ptr, col_ind, dia_ptr, ILU, invM, y, lane);
+    __syncwarp();
+  }
+}
+
+// ---- LU-SGS (CSysMatrix.cpp:826-888): thread per row within a level ----------------------------------------
+template <int NV>
+__global__ void k_lusgs_forward_level(int n, const int* __restrict__ rows, int begin, const int* __restrict__ row_ptr,
+                                      const int* __restrict__ col_ind, const int* __restrict__ dia_ptr,
+                                      const double* __restrict__ A, const double* __restrict__ b,
+                                      double* __restrict__ x) {
+  const int t = blockIdx.x * blockDim.x + threadIdx.x;
+  if (t >= n) return;
+  const int i = rows[t];
+  double low[NV];
+#pragma unroll
+  for (int r = 0; r < NV; ++r) low[r] = 0.0;
+  for (int idx = row_ptr[i]; idx < dia_ptr[i]; ++idx) {
+    const int j = col_ind[idx];
+    if (j < begin) continue;
+    const double* B = A + (size_t)idx * NV * NV;
+#pragma unroll
+    for (int r = 0; r < NV; ++r)
+#pragma unroll
+      for (int k = 0; k < NV; ++k) low[r] += B[r * NV + k] * x[(size_t)j * NV + k];
+  }
+  double v[NV], D[NV * NV];
+#pragma unroll
+  for (int r = 0; r < NV; ++r) v[r] = b[(size_t)i * NV + r] - low[r];
+  const double* Dg = A + (size_t)dia_ptr[i] * NV * NV;
+#pragma unroll
+  for (int k = 0; k < NV * NV; ++k) D[k] = Dg[k];
+  gauss_elim_d<NV>(D, v);
+#pragma unroll
+  for (int r = 0; r < NV; ++r) x[(size_t)i * NV + r] = v[r];
+}
+
+template <int NV>
+__global__ void k_lusgs_backward_level(int n, const int* __restrict__ rows, int col_ub, int Pd,
+                                       const int* __restrict__ row_ptr, const int* __restrict__ col_ind,
+                                       const int* __restrict__ dia_ptr, const double* __restrict__ A,
+                                       double* __restrict__ x) {
+  const int t = blockIdx.x * blockDim.x + threadIdx.x;
+  if (t >= n) return;
+  const int i = rows[t];
+  double up[NV], dia[NV], xi[NV], D[NV * NV];
+  const double* Dg = A + (size_t)dia_ptr[i] * NV * NV;
+#pragma unroll
+  for (int k = 0; k < NV * NV; ++k) D[k] = Dg[k];
+#pragma unroll
+  for (int r = 0; r < NV; ++r) { up[r] = 0.0; xi[r] = x[(size_t)i * NV + r]; }
+#pragma unroll
+  for (int r = 0; r < NV; ++r) {
+    double s = 0.0;
+#pragma unroll
+    for (int k = 0; k < NV; ++k) s += D[r * NV + k] * xi[k];
+    dia[r] = s;
+  }
+  for (int idx = dia_ptr[i] + 1; idx < row_ptr[i + 1]; ++idx) {
+    const int j = col_ind[idx];
+    if (j < col_ub || j >= Pd) {
+      const double* B = A + (size_t)idx * NV * NV;
+#pragma unroll
+      for (int r = 0; r < NV; ++r)
+#pragma unroll
+        for (int k = 0; k < NV; ++k) up[r] += B[r * NV + k] * x[(size_t)j * NV + k];
+    }
+  }
+  double v[NV];
+#pragma unroll
+  for (int r = 0; r < NV; ++r) v[r] = dia[r] - up[r];
+  gauss_elim_d<NV>(D, v);
+#pragma unroll
+  for (int r = 0; r < NV; ++r) x[(size_t)i * NV + r] = v[r];
+}
+
+// ------------------------------------------------------------------------------------------------
+// Host: dependency levels of the owned sub-matrix (lower: deps j<i ; upper: deps j>i, j<Pd)
+// ------------------------------------------------------------------------------------------------
+static void build_levels(LinSys& ls) {
+  if (ls.levels_ready) return;
+  const int n = ls.Pd;
+  const auto& rp = ls.h_row_ptr;
+  const auto& ci = ls.h_col_ind;
+  const auto& dp = ls.h_dia_ptr;
+  std::vector<int> lev(n, 0);
+  int nl = 0;
+  for (int i = 0; i < n; ++i) {
+    int l = 0;
+    for (int k = rp[i]; k < dp[i]; ++k) l = std::max(l, lev[ci[k]] + 1);
+    lev[i] = l;
+    nl = std::max(nl, l + 1);
+  }
+  auto bucket = [&](int nlev, std::vector<int>& ptr, dvec<int>& rows_d) {
+    ptr.assign(nlev + 1, 0);
+    for (int i = 0; i < n; ++i) ptr[lev[i] + 1]++;
+    for (int l = 0; l < nlev; ++l) ptr[l + 1] += ptr[l];
+    std::vector<int> rows(n), pos(ptr.begin(), ptr.end() - 1);
+    for (int i = 0; i < n; ++i) rows[pos[lev[i]]++] = i;
+    rows_d.upload(rows);
+  };
+  ls.nlev_lower = nl;
+  bucket(nl, ls.lvl_ptr_lower, ls.lvl_rows_lower);
+  nl = 0;
+  for (int i = n - 1; i >= 0; --i) {
+    int l = 0;
+    for (int k = dp[i] + 1; k < rp[i + 1]; ++k) {
+      if (ci[k] >= n) break;
+      l = std::max(l, lev[ci[k]] + 1);
+    }
+    lev[i] = l;
+    nl = std::max(nl, l + 1);
+  }
+  ls.nlev_upper = nl;
+  bucket(nl, ls.lvl_ptr_upper, ls.lvl_rows_upper);
+  ls.levels_ready = true;
+}
+
+// nnz-balanced partitions, CSysMatrix::Initialize (CSysMatrix.cpp:199-227)
+static void build_partitions(LinSys& ls, int nparts) {
+  if ((int)ls.h_parts.size() == nparts + 1) return;
+  const auto& rp = ls.h_row_ptr;
+  const int n = ls.Pd;
+  ls.h_parts.assign(nparts + 1, n);
+  ls.h_parts[0] = 0;
+  const long nnz_per = (long)((rp[n] + nparts - 1) / nparts);  // roundUpDiv
+  int part = 0;
+  for (int i = 0; i < n && part < nparts; ++i) {
+    if (rp[i + 1] >= nnz_per * (part + 1)) ls.h_parts[++part] = i + 1;
+  }
+  for (int p = part + 1; p <= nparts; ++p) ls.h_parts[p] = n;
+  ls.parts.upload(ls.h_parts);
+}
+
+template <int NV>
+static void ilu_build_impl(su2b200_ctx* c, LinSys& ls) {
+  const size_t nb = (size_t)ls.nnz * NV * NV;
+  ls.ilu.alloc(nb);
+  ls.invM.alloc((size_t)ls.Pd * NV * NV);
+  SU2B_CUDA(cudaMemcpyAsync(ls.ilu.p, ls.A.p, nb * sizeof(double), cudaMemcpyDeviceToDevice, c->stream));
+  if (ls.nparts <= 1) {
+    build_levels(ls);
+    for (int l = 0; l < ls.nlev_lower; ++l) {
+      const int n = ls.lvl_ptr_lower[l + 1] - ls.lvl_ptr_lower[l];
+      SU2B_LAUNCH(c, k_ilu_factor_level<NV>, nblk((long)n * 32, 128), 128, n, ls.lvl_rows_lower.p + ls.lvl_ptr_lower[l], 0,
+                  ls.Pd, ls.row_ptr, ls.col_ind, ls.dia_ptr, ls.ilu.p, ls.invM.p);
+    }
+  } else {
+    build_partitions(ls, ls.nparts);
+    SU2B_LAUNCH(c, k_ilu_factor_part<NV>, nblk((long)ls.nparts * 32, 64), 64, ls.nparts, ls.parts.p, ls.row_ptr,
+                ls.col_ind, ls.dia_ptr, ls.ilu.p, ls.invM.p);
+  }
+}
+
+template <int NV>
+static void ilu_apply_impl(su2b200_ctx* c, LinSys& ls, const double* x, double* y) {
+  const size_t n = (size_t)ls.Pd * NV;
+  if (x != y) SU2B_CUDA(cudaMemcpyAsync(y, x, n * sizeof(double), cudaMemcpyDeviceToDevice, c->stream));
+  if (ls.nparts <= 1) {
+    for (int l = 1; l < ls.nlev_lower; ++l) {
+      const int m = ls.lvl_ptr_lower[l + 1] - ls.lvl_ptr_lower[l];
+      SU2B_LAUNCH(c, k_ilu_forward_level<NV>, nblk((long)m * 32, 128), 128, m, ls.lvl_rows_lower.p + ls.lvl_ptr_lower[l], 0,
+                  ls.row_ptr, ls.col_ind, ls.dia_ptr, ls.ilu.p, y);
+    }
+    for (int l = 0; l < ls.nlev_upper; ++l) {
+      const int m = ls.lvl_ptr_upper[l + 1] - ls.lvl_ptr_upper[l];
+      SU2B_LAUNCH(c, k_ilu_backward_level<NV>, nblk((long)m * 32, 128), 128, m, ls.lvl_rows_upper.p + ls.lvl_ptr_upper[l],
+                  ls.Pd, ls.row_ptr, ls.col_ind, ls.dia_ptr, ls.ilu.p, ls.invM.p, y);
+    }
+  } else {
+    SU2B_LAUNCH(c, k_ilu_apply_part<NV>, nblk((long)ls.nparts * 32, 64), 64, ls.nparts, ls.parts.p, ls.row_ptr, ls.col_ind,
+                ls.dia_ptr, ls.ilu.p, ls.invM.p, y);
+  }
+}
+
+void linsys_build_ilu(su2b200_ctx* c, LinSys& ls) {
+  switch (ls.nVar) {
+    case 1: ilu_build_impl<1>(c, ls); break;
+    case 4: ilu_build_impl<4>(c, ls); break;
+    case 5: ilu_build_impl<5>(c, ls); break;
+    default: throw Error("ilu: unsupported nVar");
+  }
+}
+void linsys_apply_ilu(su2b200_ctx* c, LinSys& ls, const double* x, double* y) {
+  switch (ls.nVar) {
+    case 1: ilu_apply_impl<1>(c, ls, x, y); break;
+    case 4: ilu_apply_impl<4>(c, ls, x, y); break;
+    case 5: ilu_apply_impl<5>(c, ls, x, y); break;
+    default: throw Error("ilu: unsupported nVar");
+  }
+  if (c->nranks > 1) halo_exchange(c, y, ls.nVar);
+}
+
+template <int NV>
+static void lusgs_impl(su2b200_ctx* c, LinSys& ls, const double* b, double* x) {
+  build_levels(ls);
+  for (int l = 0; l < ls.nlev_lower; ++l) {
+    const int m = ls.lvl_ptr_lower[l + 1] - ls.lvl_ptr_lower[l];
+    SU2B_LAUNCH(c, k_lusgs_forward_level<NV>, nblk(m, 128), 128, m, ls.lvl_rows_lower.p + ls.lvl_ptr_lower[l], 0, ls.row_ptr,
+                ls.col_ind, ls.dia_ptr, ls.A.p, b, x);
+  }
+  if (c->nranks > 1) halo_exchange(c, x, NV);
+  for (int l = 0; l < ls.nlev_upper; ++l) {
+    const int m = ls.lvl_ptr_upper[l + 1] - ls.lvl_ptr_upper[l];
+    SU2B_LAUNCH(c, k_lusgs_backward_level<NV>, nblk(m, 128), 128, m, ls.lvl_rows_upper.p + ls.lvl_ptr_upper[l], ls.Pd, ls.Pd,
+                ls.row_ptr, ls.col_ind, ls.dia_ptr, ls.A.p, x);
+  }
+  if (c->nranks > 1) halo_exchange(c, x, NV);
+}
+
+void linsys_apply_lusgs(su2b200_ctx* c, LinSys& ls, const double* b, double* x) {
+  SU2B_REQUIRE(b != x, "LU-SGS needs distinct input and output vectors");
+  switch (ls.nVar) {
+    case 1: lusgs_impl<1>(c, ls, b, x); break;
+    case 4: lusgs_impl<4>(c, ls, b, x); break;
+    case 5: lusgs_impl<5>(c, ls, b, x); break;
+    default: throw Error("lusgs: unsupported nVar");
+  }
+}
+
+void linsys_build_prec(su2b200_ctx* c, LinSys& ls, int prec) {
+  switch (prec) {
+    case SU2B200_PREC_JACOBI: linsys_build_jacobi(c, ls); break;
+    case SU2B200_PREC_ILU: linsys_build_ilu(c, ls); break;
+    case SU2B200_PREC_LU_SGS: break;
+    default: throw Error("unknown preconditioner");
+  }
+}
+void linsys_apply_prec(su2b200_ctx* c, LinSys& ls, int prec, const double* x, double* y) {
+  switch (prec) {
+    case SU2B200_PREC_JACOBI: linsys_apply_jacobi(c, ls, x, y); break;
+    case SU2B200_PREC_ILU: linsys_apply_ilu(c, ls, x, y); break;
+    case SU2B200_PREC_LU_SGS: linsys_apply_lusgs(c, ls, x, y); break;
+    default: throw Error("unknown preconditioner");
+  }
+}
+
+}  // namespace su2b200
