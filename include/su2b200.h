@@ -93,6 +93,8 @@ int su2b200_destroy(su2b200_ctx* ctx);
 const char* su2b200_last_error(void);
 int su2b200_version(void);
 int su2b200_synchronize(su2b200_ctx* ctx);
+/* sizeof() of the three POD structs of this header, so that FFI bindings can verify their layout */
+int su2b200_struct_sizes(int* geometry_desc, int* flow_config, int* iter_report);
 
 /* ---- geometry: CGeometry dual grid + sparse pattern --------------------------------- */
 
@@ -260,6 +262,9 @@ int su2b200_iterate(su2b200_ctx* ctx, int nIter, su2b200_iter_report* reports /*
  * creates system `which` of the context from a pattern. Geometry upload does this implicitly. */
 int su2b200_linsys_create(su2b200_ctx* ctx, int which, int nVar, unsigned long nPoint, unsigned long nPointDomain,
                           const unsigned long* row_ptr, const unsigned long* col_ind);
+/* number of row partitions of the preconditioner sweeps: LINEAR_SOLVER_PREC_THREADS / omp_partitions
+ * (CSysMatrix.cpp:199-227); 1 = the serial reference order (level-scheduled on the device) */
+int su2b200_linsys_set_partitions(su2b200_ctx* ctx, int which, int nparts);
 /* CSysMatrix::HtDTransfer (CSysMatrixGPU.cu:59-64) */
 int su2b200_linsys_set_matrix(su2b200_ctx* ctx, int which, const double* blocks);
 /* CSysMatrix::GPUMatrixVectorProduct (CSysMatrixGPU.cu:66-86) == MatrixVectorProduct (CSysMatrix.cpp:617-645):

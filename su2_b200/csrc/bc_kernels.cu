@@ -102,10 +102,7 @@ __global__ void k_bc_far_field(int nV, int Pd, FlowParams p, FarFieldInf inf, co
 #pragma unroll
       for (int k = 0; k < NV * NV; ++k) jac_i[k] = 0.0;
     } else {
-      FlowParams q = p;
-      q.roe_kappa = 0.5;  // legacy functor: kappa hard-wired through GetRoe_Kappa too; same value
-      q.roe_kappa = p.roe_kappa;
-      roe_flux<ND, true>(q, Vd, Vj, normal, flux, jac_i, jac_j);
+      roe_flux<ND, true>(p, Vd, Vj, normal, flux, jac_i, jac_j);
     }
   }
   double* D = A + (size_t)dia_ptr[i] * NV * NV;
@@ -283,6 +280,99 @@ void flow_bc_heatflux_wall(su2b200_ctx* c, int iMarker) {
     SU2B_LAUNCH(c, k_bc_heatflux_wall<2>, nb, 64, m.nVertex, g.Pd, m.heat_flux, m.node.p, m.normal.p, g.row_ptr.p, g.dia_ptr.p, s.U_old.p, s.res.p, c->sys[0].A.p);
   else
     SU2B_LAUNCH(c, k_bc_heatflux_wall<3>, nb, 64, m.nVertex, g.Pd, m.heat_flux, m.node.p, m.normal.p, g.row_ptr.p, g.dia_ptr.p, s.U_old.p, s.res.p, c->sys[0].A.p);
+}
+
+}  // namespace su2b200
+
+// ------------------------------------------------------------------------------------------------
+// a29. CFVMFlowSolverBase::Pressure_Forces (CFVMFlowSolverBase.inl:1784-2100): per-vertex force and moment,
+// then a deterministic single-block reduction. out6 = (Fx,Fy,Fz,Mx,My,Mz) already scaled by 1/AeroCoeffForceRef.
+// ------------------------------------------------------------------------------------------------
+namespace su2b200 {
+
+template <int ND>
+__global__ void k_pressure_force(int nV, int Pd, double p_inf, double factor, double ref_len, double ox, double oy,
+                                 double oz, const int* __restrict__ vnode, const double* __restrict__ vnormal,
+                                 const double* __restrict__ coord, const double* __restrict__ V,
+                                 double* __restrict__ out /*[nV][6]*/) {
+  using I = PrimIdx<ND>;
+  const int t = blockIdx.x * blockDim.x + threadIdx.x;
+  if (t >= nV) return;
+  const int i = vnode[t];
+  double f[3] = {0, 0, 0}, m[3] = {0, 0, 0};
+  if (i < Pd) {
+    const double pres = V[(size_t)i * I::NPRIM + I::P];
+    double x[3] = {0, 0, 0};
+    const double o[3] = {ox, oy, oz};
+    double md[3] = {0, 0, 0};
+#pragma unroll
+    for (int d = 0; d < ND; ++d) {
+      x[d] = coord[(size_t)i * ND + d];
+      md[d] = x[d] - o[d];
+      f[d] = -(pres - p_inf) * vnormal[(size_t)t * ND + d] * factor;
+    }
+    if (ND == 3) {
+      m[0] = (f[2] * md[1] - f[1] * md[2]) / ref_len;
+      m[1] = (f[0] * md[2] - f[2] * md[0]) / ref_len;
+    }
+    m[2] = (f[1] * md[0] - f[0] * md[1]) / ref_len;
+  }
+#pragma unroll
+  for (int k = 0; k < 3; ++k) { out[(size_t)t * 6 + k] = f[k]; out[(size_t)t * 6 + 3 + k] = m[k]; }
+}
+
+// sequential-in-thread sum over vertices (vertex order == reference order), 6 threads
+__global__ void k_force_sum(int nV, const double* __restrict__ in, double* __restrict__ acc6) {
+  const int k = threadIdx.x;
+  if (k >= 6) return;
+  double s = 0.0;
+  for (int t = 0; t < nV; ++t) s += in[(size_t)t * 6 + k];
+  acc6[k] = s;
+}
+
+void flow_forces(su2b200_ctx* c, double* coeffs) {
+  auto& g = c->geo;
+  auto& s = c->fs;
+  const auto& cfg = c->cfg;
+  double v2 = 0.0;
+  for (int d = 0; d < g.nDim; ++d) v2 += cfg.velocity_inf[d] * cfg.velocity_inf[d];
+  const double force_ref = 0.5 * cfg.density_inf * cfg.ref_area * v2;  // SetReferenceValues
+  const double factor = 1.0 / force_ref;
+  const double PI = 3.14159265358979323846;
+  const double alpha = cfg.aoa_deg * PI / 180.0, beta = cfg.aos_deg * PI / 180.0;
+  double CL = 0, CD = 0, CSF = 0, CF[3] = {0, 0, 0}, CM[3] = {0, 0, 0};
+  for (auto& m : g.markers) {
+    if (!m.monitoring || m.nVertex == 0) continue;
+    const size_t need = (size_t)m.nVertex * 6 + 8;
+    if (s.red.n < need) s.red.alloc(need);
+    double* buf = s.red.p;
+    double* acc = s.red.p + (size_t)m.nVertex * 6;
+    const int nb = nblk(m.nVertex, 128);
+    if (g.nDim == 2)
+      SU2B_LAUNCH(c, k_pressure_force<2>, nb, 128, m.nVertex, g.Pd, cfg.pressure_inf, factor, cfg.ref_length,
+                  cfg.ref_origin[0], cfg.ref_origin[1], cfg.ref_origin[2], m.node.p, m.normal.p, g.coord.p, s.V.p, buf);
+    else
+      SU2B_LAUNCH(c, k_pressure_force<3>, nb, 128, m.nVertex, g.Pd, cfg.pressure_inf, factor, cfg.ref_length,
+                  cfg.ref_origin[0], cfg.ref_origin[1], cfg.ref_origin[2], m.node.p, m.normal.p, g.coord.p, s.V.p, buf);
+    SU2B_LAUNCH(c, k_force_sum, 1, 32, m.nVertex, buf, acc);
+    SU2B_CUDA(cudaMemcpyAsync(s.h_red, acc, 6 * sizeof(double), cudaMemcpyDeviceToHost, c->stream));
+    SU2B_CUDA(cudaStreamSynchronize(c->stream));
+    const double* F = s.h_red;
+    if (g.nDim == 2) {
+      CD += F[0] * cos(alpha) + F[1] * sin(alpha);
+      CL += -F[0] * sin(alpha) + F[1] * cos(alpha);
+    } else {
+      CD += F[0] * cos(alpha) * cos(beta) + F[1] * sin(beta) + F[2] * sin(alpha) * cos(beta);
+      CL += -F[0] * sin(alpha) + F[2] * cos(alpha);
+      CSF += -F[0] * sin(beta) * cos(alpha) + F[1] * cos(beta) - F[2] * sin(beta) * sin(alpha);
+    }
+    for (int k = 0; k < 3; ++k) { CF[k] += F[k]; CM[k] += F[3 + k]; }
+  }
+  if (coeffs) {
+    coeffs[0] = CL; coeffs[1] = CD; coeffs[2] = CSF;
+    coeffs[3] = CF[0]; coeffs[4] = CF[1]; coeffs[5] = CF[2];
+    coeffs[6] = CM[0]; coeffs[7] = CM[1]; coeffs[8] = CM[2];
+  }
 }
 
 }  // namespace su2b200

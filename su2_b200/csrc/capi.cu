@@ -36,6 +36,12 @@ extern "C" {
 
 const char* su2b200_last_error(void) { return g_last_error.c_str(); }
 int su2b200_version(void) { return 100; }
+int su2b200_struct_sizes(int* g, int* f, int* r) {
+  if (g) *g = (int)sizeof(su2b200_geometry_desc);
+  if (f) *f = (int)sizeof(su2b200_flow_config);
+  if (r) *r = (int)sizeof(su2b200_iter_report);
+  return 0;
+}
 
 int su2b200_create(int device, su2b200_ctx** out) {
   API_BEGIN

@@ -1,0 +1,144 @@
+// a28. Halo exchange and global reductions: CSolver::InitiateComms/CompleteComms (SU2_CFD/src/solvers/CSolver.cpp:1406-1697),
+// CSysMatrixComms (Common/src/linear_algebra/CSysMatrix.cpp:251-477), tables of CGeometry::PreprocessP2PComms
+// (Common/src/geometry/CGeometry.cpp:139-332). Device pack -> ncclSend/ncclRecv group -> device unpack.
+// NCCL is resolved at run time with dlopen (libnccl.so.2: the copy torch already loaded, or the system one), so
+// the single-GPU path has no NCCL dependency.
+#include "internal.hpp"
+#include "kernels.hpp"
+#include <dlfcn.h>
+
+namespace su2b200 {
+
+static inline int nblk(long n, int bs) { return (int)((n + bs - 1) / bs); }
+
+// minimal NCCL ABI (nccl.h 2.x): opaque comm, 128-byte unique id, ncclFloat64 = 8, ncclSum = 0
+struct NcclApi {
+  void* lib = nullptr;
+  int (*GetUniqueId)(void*) = nullptr;
+  int (*CommInitRank)(void**, int, unsigned char[128], int) = nullptr;  // id passed by value (128-byte struct)
+  int (*CommDestroy)(void*) = nullptr;
+  int (*Send)(const void*, size_t, int, int, void*, cudaStream_t) = nullptr;
+  int (*Recv)(void*, size_t, int, int, void*, cudaStream_t) = nullptr;
+  int (*AllReduce)(const void*, void*, size_t, int, int, void*, cudaStream_t) = nullptr;
+  int (*GroupStart)() = nullptr;
+  int (*GroupEnd)() = nullptr;
+  const char* (*GetErrorString)(int) = nullptr;
+};
+struct NcclId { unsigned char b[128]; };
+
+static NcclApi& nccl() {
+  static NcclApi api;
+  if (api.lib) return api;
+  const char* names[] = {"libnccl.so.2", "libnccl.so"};
+  for (const char* n : names) {
+    api.lib = dlopen(n, RTLD_NOW | RTLD_GLOBAL);
+    if (api.lib) break;
+  }
+  if (!api.lib) throw Error("NCCL not found (dlopen libnccl.so.2 failed): multi-GPU runs need it");
+  auto sym = [&](const char* s) {
+    void* p = dlsym(api.lib, s);
+    if (!p) throw Error(std::string("NCCL symbol missing: ") + s);
+    return p;
+  };
+  api.GetUniqueId = (int (*)(void*))sym("ncclGetUniqueId");
+  api.CommInitRank = (int (*)(void**, int, unsigned char[128], int))sym("ncclCommInitRank");
+  api.CommDestroy = (int (*)(void*))sym("ncclCommDestroy");
+  api.Send = (int (*)(const void*, size_t, int, int, void*, cudaStream_t))sym("ncclSend");
+  api.Recv = (int (*)(void*, size_t, int, int, void*, cudaStream_t))sym("ncclRecv");
+  api.AllReduce = (int (*)(const void*, void*, size_t, int, int, void*, cudaStream_t))sym("ncclAllReduce");
+  api.GroupStart = (int (*)())sym("ncclGroupStart");
+  api.GroupEnd = (int (*)())sym("ncclGroupEnd");
+  api.GetErrorString = (const char* (*)(int))sym("ncclGetErrorString");
+  return api;
+}
+#define SU2B_NCCL(call)                                                                         \
+  do {                                                                                          \
+    int r_ = (call);                                                                            \
+    if (r_ != 0) throw Error(std::string(#call) + " failed: " + nccl().GetErrorString(r_));     \
+  } while (0)
+
+__global__ void k_pack(int n, int cnt, const int* __restrict__ idx, const double* __restrict__ arr,
+                       double* __restrict__ buf) {
+  const int t = blockIdx.x * blockDim.x + threadIdx.x;
+  if (t >= n * cnt) return;
+  const int p = t / cnt, k = t % cnt;
+  buf[t] = arr[(size_t)idx[p] * cnt + k];
+}
+__global__ void k_unpack(int n, int cnt, const int* __restrict__ idx, const double* __restrict__ buf,
+                         double* __restrict__ arr) {
+  const int t = blockIdx.x * blockDim.x + threadIdx.x;
+  if (t >= n * cnt) return;
+  const int p = t / cnt, k = t % cnt;
+  arr[(size_t)idx[p] * cnt + k] = buf[t];
+}
+
+void halo_exchange(su2b200_ctx* c, double* arr, int cnt) {
+  if (c->nranks <= 1 || c->p2p_ranks.empty()) return;
+  SU2B_REQUIRE(c->nccl, "halo exchange requested without a communicator (su2b200_comm_init)");
+  const int nn = (int)c->p2p_ranks.size();
+  const int nsend = c->p2p_send_ptr[nn], nrecv = c->p2p_recv_ptr[nn];
+  if (c->p2p_send_buf.n < (size_t)nsend * cnt) c->p2p_send_buf.alloc((size_t)nsend * cnt);
+  if (c->p2p_recv_buf.n < (size_t)nrecv * cnt) c->p2p_recv_buf.alloc((size_t)nrecv * cnt);
+  SU2B_LAUNCH(c, k_pack, nblk((long)nsend * cnt, 256), 256, nsend, cnt, c->p2p_send_idx.p, arr, c->p2p_send_buf.p);
+  auto& api = nccl();
+  SU2B_NCCL(api.GroupStart());
+  for (int k = 0; k < nn; ++k) {
+    const int ns = c->p2p_send_ptr[k + 1] - c->p2p_send_ptr[k], nr = c->p2p_recv_ptr[k + 1] - c->p2p_recv_ptr[k];
+    if (nr) SU2B_NCCL(api.Recv(c->p2p_recv_buf.p + (size_t)c->p2p_recv_ptr[k] * cnt, (size_t)nr * cnt, 8, c->p2p_ranks[k], c->nccl, c->stream));
+    if (ns) SU2B_NCCL(api.Send(c->p2p_send_buf.p + (size_t)c->p2p_send_ptr[k] * cnt, (size_t)ns * cnt, 8, c->p2p_ranks[k], c->nccl, c->stream));
+  }
+  SU2B_NCCL(api.GroupEnd());
+  SU2B_LAUNCH(c, k_unpack, nblk((long)nrecv * cnt, 256), 256, nrecv, cnt, c->p2p_recv_idx.p, c->p2p_recv_buf.p, arr);
+}
+
+double allreduce_sum(su2b200_ctx* c, double v) {
+  if (c->nranks <= 1) return v;
+  SU2B_REQUIRE(c->nccl, "allreduce requested without a communicator");
+  if (c->p2p_send_buf.n < 2) c->p2p_send_buf.alloc(64);
+  double* d = c->p2p_send_buf.p;
+  SU2B_CUDA(cudaMemcpyAsync(d, &v, sizeof(double), cudaMemcpyHostToDevice, c->stream));
+  SU2B_NCCL(nccl().AllReduce(d, d, 1, 8, 0, c->nccl, c->stream));
+  double out = 0;
+  SU2B_CUDA(cudaMemcpyAsync(&out, d, sizeof(double), cudaMemcpyDeviceToHost, c->stream));
+  SU2B_CUDA(cudaStreamSynchronize(c->stream));
+  return out;
+}
+
+}  // namespace su2b200
+
+using namespace su2b200;
+extern "C" {
+int su2b200_comm_unique_id(unsigned char id[128]) {
+  try {
+    SU2B_NCCL(nccl().GetUniqueId(id));
+    return 0;
+  } catch (const std::exception& e) { set_error(e.what()); return 1; }
+}
+int su2b200_comm_init(su2b200_ctx* c, int rank, int size, const unsigned char id[128]) {
+  try {
+    if (!c) throw Error("null context");
+    SU2B_CUDA(cudaSetDevice(c->device));
+    c->rank = rank;
+    c->nranks = size;
+    if (size > 1) {
+      NcclId nid;
+      memcpy(nid.b, id, 128);
+      // ncclCommInitRank(ncclComm_t*, int nranks, ncclUniqueId commId (by value), int rank)
+      auto fn = (int (*)(void**, int, NcclId, int))dlsym(nccl().lib, "ncclCommInitRank");
+      SU2B_NCCL(fn(&c->nccl, size, nid, rank));
+    }
+    return 0;
+  } catch (const std::exception& e) { set_error(e.what()); return 1; }
+}
+int su2b200_halo_exchange(su2b200_ctx* c, int which) {
+  try {
+    if (!c) throw Error("null context");
+    double* p = nullptr;
+    size_t n = 0;
+    long sz = su2b200_array_size(c, which);
+    if (sz < 0) throw Error("unknown array id");
+    (void)p; (void)n;
+    throw Error("su2b200_halo_exchange: use the solver entry points (exchange happens inside them)");
+  } catch (const std::exception& e) { set_error(e.what()); return 1; }
+}
+}

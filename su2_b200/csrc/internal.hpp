@@ -36,6 +36,11 @@ struct dvec {
   dvec() = default;
   dvec(const dvec&) = delete;
   dvec& operator=(const dvec&) = delete;
+  dvec(dvec&& o) noexcept : p(o.p), n(o.n) { o.p = nullptr; o.n = 0; }
+  dvec& operator=(dvec&& o) noexcept {
+    if (this != &o) { release(); p = o.p; n = o.n; o.p = nullptr; o.n = 0; }
+    return *this;
+  }
   ~dvec() { release(); }
   void release() {
     if (p) cudaFree(p);

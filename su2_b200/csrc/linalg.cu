@@ -296,3 +296,4 @@ void linsys_apply_jacobi(su2b200_ctx* c, LinSys& ls, const double* x, double* y)
   }
   if (c->nranks > 1) halo_exchange(c, y, ls.nVar);
 }
+}  // namespace su2b200

@@ -1,0 +1,101 @@
+"""Helpers shared by the parity tests: drive the CUDA path through the C ABI in the reference's call order
+and compare every stage with the golden arrays produced by the unmodified reference (oracle/make_golden.py)."""
+import os
+import numpy as np
+
+from oracle.dumpio import load_golden, geometry_from_dump, config_from_dump
+from su2_b200 import capi
+from su2_b200.solver import FlowSolver
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+def relerr(a, b):
+    a = np.asarray(a, dtype=np.float64).ravel()
+    b = np.asarray(b, dtype=np.float64).ravel()
+    assert a.shape == b.shape, (a.shape, b.shape)
+    scale = np.max(np.abs(b))
+    if scale == 0.0:
+        return float(np.max(np.abs(a)))
+    return float(np.max(np.abs(a - b)) / scale)
+
+
+def make_solver(gold, **overrides):
+    s = FlowSolver(0)
+    s.set_geometry(geometry_from_dump(gold))
+    kw = config_from_dump(gold)
+    kw.update(overrides)
+    s.configure(**kw)
+    s.allocate()
+    return s
+
+
+def run_first_iteration(s, gold, it=0, report=None, check=None):
+    """One implicit iteration stage by stage; `check(name, got, key)` is called for every comparable array."""
+    pre = "it%d_" % it
+    nd, P, nv = s.nDim, s.nPoint, s.nVar
+    ng = nd + 2
+    kinds = [m["kind"] for m in s.markers]
+
+    def cmp(name, got, key, sl=None):
+        if key not in gold:
+            return
+        ref = gold[key]
+        if sl is not None:
+            got, ref = sl(np.asarray(got)), sl(np.asarray(ref))
+        e = relerr(got, ref)
+        if report is not None:
+            report[name] = e
+        if check is not None:
+            check(name, e)
+
+    s.Preprocessing(False)
+    cmp("primitive", s.get("PRIMITIVE").reshape(P, nd + 9)[:, :nd + 5], pre + "pre_primitive", lambda a: a.reshape(P, -1)[:, :nd + 5])
+    if s.cfg.viscous:
+        cmp("primitive_visc", s.get("PRIMITIVE").reshape(P, nd + 9), pre + "pre_primitive")
+        cmp("grad_prim", s.get("GRAD_PRIM").reshape(P, ng, nd)[:s.nPointDomain], pre + "pre_grad_prim",
+            lambda a: a.reshape(P, ng, nd)[:s.nPointDomain])
+    if s.cfg.conv_scheme == capi.CONV_JST:
+        cmp("lambda", s.get("LAMBDA"), pre + "pre_lambda")
+        cmp("sensor", s.get("SENSOR"), pre + "pre_sensor")
+        cmp("und_lapl", s.get("UND_LAPL"), pre + "pre_und_lapl")
+    elif s.cfg.muscl:
+        cmp("grad_recon", s.get("GRAD_RECON"), pre + "pre_grad_recon")
+        if s.cfg.limiter != capi.LIMITER_NONE:
+            cmp("limiter", s.get("LIMITER"), pre + "pre_limiter")
+    s.Set_OldSolution()
+    mn, mx = s.SetTime_Step()
+    cmp("delta_time", s.get("DELTA_TIME"), pre + "delta_time")
+    cmp("min_dt", [mn], pre + "min_dt")
+    s.EdgeFluxResidual()
+    cmp("edge_residual", s.get("LINSYSRES"), pre + "edge_linsysres")
+    cmp("edge_jacobian", s.get("JACOBIAN"), pre + "edge_jacobian")
+    for m, k in enumerate(kinds):
+        if k == capi.FAR_FIELD:
+            s.BC_Far_Field(m)
+    cmp("far_residual", s.get("LINSYSRES"), pre + "far_linsysres")
+    for m, k in enumerate(kinds):
+        if k == capi.HEAT_FLUX:
+            s.BC_HeatFlux_Wall(m)
+    for m, k in enumerate(kinds):
+        if k in (capi.SYMMETRY_PLANE, capi.EULER_WALL):
+            s.BC_Sym_Plane(m)
+    cmp("bc_residual", s.get("LINSYSRES"), pre + "bc_linsysres")
+    cmp("bc_jacobian", s.get("JACOBIAN"), pre + "bc_jacobian")
+    cmp("bc_solution_old", s.get("SOLUTION_OLD"), pre + "bc_solution_old")
+    rms, _, _ = s.PrepareImplicitIteration()
+    cmp("rhs", s.get("LINSYSRES"), pre + "sys_linsysres")
+    cmp("sys_jacobian", s.get("JACOBIAN"), pre + "sys_jacobian")
+    cmp("res_rms", rms, pre + "res_rms")
+    iters, res = s.Solve()
+    if pre + "ilu" in gold:
+        cmp("ilu", s.get("ILU"), pre + "ilu")
+        cmp("invM", s.get("INVM"), pre + "invM")
+    cmp("linsyssol", s.get("LINSYSSOL"), pre + "linsyssol")
+    if report is not None:
+        report["linsol_iter"] = (iters, int(gold.get(pre + "linsol_iter", -1)))
+    s.CompleteImplicitIteration()
+    cmp("post_solution", s.get("SOLUTION"), pre + "post_solution")
+    cmp("under_relax", s.get("UNDER_RELAX"), pre + "under_relax")
+    s.Preprocessing(True)
+    return rms
