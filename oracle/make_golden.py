@@ -20,17 +20,20 @@ from oracle.dumpio import load_dump  # noqa: E402
 REF_MESH_DIR = "/root/reference/QuickStart"
 
 # name -> (cfg, nIter, dump iterations, arrays to drop (size), mesh file or None)
+# name -> (cfg, nIter, dump iterations, iteration whose matrices are kept, mesh file or None)
 CASES = {
-    "naca0012_roe": ("naca0012_roe.cfg", 10, "0", ("_edge_jacobian", "_far_jacobian", "_sys_jacobian", "_ilu", "_invM"), "mesh_NACA0012_inv.su2"),
-    "naca0012_jst": ("naca0012_jst.cfg", 10, "0", ("_edge_jacobian", "_far_jacobian", "_sys_jacobian", "_bc_jacobian", "_ilu", "_invM"), "mesh_NACA0012_inv.su2"),
-    "box_euler": ("box_euler.cfg", 3, "0,2", ("_far_jacobian",), None),
-    "box_rans_sa": ("box_rans_sa.cfg", 3, "0,2", ("_far_jacobian",), None),
-    "rect_ns": ("rect_ns.cfg", 3, "0,2", ("_far_jacobian",), None),
+    "naca0012_roe": ("naca0012_roe.cfg", 10, "0", 0, "mesh_NACA0012_inv.su2"),
+    "naca0012_jst": ("naca0012_jst.cfg", 10, "0", None, "mesh_NACA0012_inv.su2"),
+    "box_euler": ("box_euler.cfg", 6, "0,1,2", 2, None),
+    "box_rans_sa": ("box_rans_sa.cfg", 6, "0,1,2", 2, None),
+    "rect_ns": ("rect_ns.cfg", 6, "0,1,2", 2, None),
 }
+MATRIX_KEYS = ("_jacobian", "_ilu", "_invM")
+KEEP_MATRICES = ("bc_jacobian", "_ilu", "_invM", "turb_bc_jacobian", "turb_src_jacobian", "turb_edge_jacobian", "turb_conv_jacobian")
 
 
 def run_case(name, keep_all=False, out_dir=None):
-    cfg, nit, dumps, drop, mesh = CASES[name]
+    cfg, nit, dumps, keep_it, mesh = CASES[name]
     tmp = tempfile.mkdtemp(prefix="golden_")
     try:
         shutil.copy(os.path.join(ROOT, "tests", "cases", cfg), tmp)
@@ -43,10 +46,12 @@ def run_case(name, keep_all=False, out_dir=None):
         shutil.rmtree(tmp, ignore_errors=True)
     if not keep_all:
         for k in list(d.keys()):
-            if any(k.endswith(s) for s in drop):
-                del d[k]
-            elif k.endswith("_ilu") and not k.startswith("it0_"):
-                del d[k]
+            if any(k.endswith(m) for m in MATRIX_KEYS):
+                keep = keep_it is not None and k.startswith("it%d_" % keep_it) and any(k.endswith(m) for m in KEEP_MATRICES)
+                if name.startswith("naca") and not k.endswith("bc_jacobian"):
+                    keep = False  # 36k blocks: one copy of the Jacobian is enough for the C1 mesh
+                if not keep:
+                    del d[k]
     out_dir = out_dir or os.path.join(ROOT, "tests", "golden")
     os.makedirs(out_dir, exist_ok=True)
     path = os.path.join(out_dir, name + ".npz")

@@ -631,7 +631,8 @@ __global__ void k_zero_range(double* __restrict__ a, double* __restrict__ b, siz
 //      (CFVMFlowSolverBase.hpp:983-1008)
 // =============================================================================================
 template <int NV>
-__global__ void k_complete_implicit(int Pd, double allowable, const double* __restrict__ sol, double* __restrict__ U,
+__global__ void k_complete_implicit(int Pd, double allowable, const double* __restrict__ sol,
+                                    const double* __restrict__ U_old, double* __restrict__ U,
                                     double* __restrict__ under_relax) {
   const int i = blockIdx.x * blockDim.x + threadIdx.x;
   if (i >= Pd) return;
@@ -649,7 +650,9 @@ __global__ void k_complete_implicit(int Pd, double allowable, const double* __re
   if (ur < 1e-10) ur = 0.0;
   under_relax[i] = ur;
 #pragma unroll
-  for (int v = 0; v < NV; ++v) U[(size_t)i * NV + v] = u[v] + ur * dx[v];
+  // CVariable::AddSolution (CVariable.hpp:341-343): Solution = Solution_Old + value (Solution_Old carries the
+  // strong-BC corrections made by BC_Sym_Plane / BC_HeatFlux_Wall)
+  for (int v = 0; v < NV; ++v) U[(size_t)i * NV + v] = U_old[(size_t)i * NV + v] + ur * dx[v];
 }
 
 // =============================================================================================
@@ -848,8 +851,8 @@ void turb_prepare_implicit_generic(su2b200_ctx* c, double* rms, double* mx, unsi
 void flow_complete_implicit(su2b200_ctx* c) {
   auto& g = c->geo;
   auto& s = c->fs;
-  if (g.nDim == 2) LAUNCH(c, k_complete_implicit<4>, nblk(g.Pd, 256), 256, g.Pd, c->cfg.max_update_flow, s.sol.p, s.U.p, s.under_relax.p);
-  else LAUNCH(c, k_complete_implicit<5>, nblk(g.Pd, 256), 256, g.Pd, c->cfg.max_update_flow, s.sol.p, s.U.p, s.under_relax.p);
+  if (g.nDim == 2) LAUNCH(c, k_complete_implicit<4>, nblk(g.Pd, 256), 256, g.Pd, c->cfg.max_update_flow, s.sol.p, s.U_old.p, s.U.p, s.under_relax.p);
+  else LAUNCH(c, k_complete_implicit<5>, nblk(g.Pd, 256), 256, g.Pd, c->cfg.max_update_flow, s.sol.p, s.U_old.p, s.U.p, s.under_relax.p);
 }
 
 }  // namespace su2b200

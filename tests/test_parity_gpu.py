@@ -27,23 +27,36 @@ def _gold(name):
     return load_golden(p)
 
 
+def _dump_iters(gold):
+    its = sorted({int(k[2:k.index("_")]) for k in gold if k.startswith("it") and k.endswith("_pre_solution")})
+    return its
+
+
 @pytest.mark.parametrize("case", CASES)
-def test_first_iteration_stage_by_stage(case):
+def test_iteration_stage_by_stage(case):
+    """Every stage of one implicit iteration against the reference, at the first and the last dumped iteration."""
     gold = _gold(case)
-    s = make_solver(gold)
-    report = {}
-    run_first_iteration(s, gold, 0, report)
-    s.close()
-    print(case, {k: ("%.2e" % v if isinstance(v, float) else v) for k, v in report.items()})
-    bad = {k: v for k, v in report.items() if isinstance(v, float) and not (v <= TOL.get(k, TOL["default"]))}
-    assert not bad, bad
-    it, ref_it = report["linsol_iter"]
-    assert it == ref_it
+    if gold["cfg_rans_sa"]:
+        pytest.skip("flow part of the RANS case is covered by test_rans_sa")
+    its = _dump_iters(gold)
+    for it in sorted({its[0], its[-1]}):
+        s = make_solver(gold)
+        report = {}
+        run_first_iteration(s, gold, it, report)
+        s.close()
+        print(case, "it", it, {k: ("%.2e" % v if isinstance(v, float) else v) for k, v in report.items()})
+        bad = {k: v for k, v in report.items() if isinstance(v, float) and not (v <= TOL.get(k, TOL["default"]))}
+        assert not bad, (it, bad)
+        got, ref = report["linsol_iter"]
+        assert got == ref, (it, got, ref)
 
 
 @pytest.mark.parametrize("case", CASES)
 def test_history_tracks_reference(case):
+    """rms residuals, CL, CD of the first iterations follow the reference's history."""
     gold = _gold(case)
+    if gold["cfg_rans_sa"]:
+        pytest.skip("covered by test_rans_sa")
     s = make_solver(gold)
     n = int(gold["nIter"])
     reps = s.iterate(n)
@@ -52,11 +65,8 @@ def test_history_tracks_reference(case):
     nv = s.nVar
     for i, r in enumerate(reps):
         ref_rms = hist[i, :nv]
-        assert np.allclose(np.log10(r["rms_flow"]), np.log10(ref_rms), atol=1e-6), (i, r["rms_flow"], ref_rms)
-        assert abs(r["CL"] - hist[i, 6]) <= 1e-6 * max(1.0, abs(hist[i, 6])), (i, r["CL"], hist[i, 6])
-        assert abs(r["CD"] - hist[i, 7]) <= 1e-6 * max(1.0, abs(hist[i, 7])), (i, r["CD"], hist[i, 7])
-    assert relerr(s_final(reps, gold, s), 0) == 0 or True
-
-
-def s_final(reps, gold, s):
-    return [0.0]
+        ok = np.abs(r["rms_flow"] - ref_rms) <= 1e-6 * np.abs(ref_rms) + 1e-15
+        assert ok.all(), (i, r["rms_flow"], ref_rms)
+        assert abs(r["CL"] - hist[i, 6]) <= 1e-6 * max(1e-3, abs(hist[i, 6])), (i, r["CL"], hist[i, 6])
+        assert abs(r["CD"] - hist[i, 7]) <= 1e-6 * max(1e-3, abs(hist[i, 7])), (i, r["CD"], hist[i, 7])
+        assert r["linsol_iter_flow"] == int(hist[i, 8]), (i, r["linsol_iter_flow"], hist[i, 8])
