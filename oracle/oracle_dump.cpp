@@ -222,7 +222,8 @@ class Dumper : public CSinglezoneDriver {
     dump_matrix(w, pre + "solution", nodes->GetSolution(), P, nVar);
     dump_matrix(w, pre + "solution_old", nodes->Solution_Old, P, nVar);
     dump_matrix(w, pre + "primitive", nodes->GetPrimitive(), P, nPrim);
-    const unsigned long ng = nDim + 2;
+    // gradient containers hold nPrimVarGrad variables (nDim+1 for centred schemes, CEulerVariable.cpp:31-42)
+    const unsigned long ng = nodes->GetGradient_Primitive().rows();
     CConfig* c = config_container[ZONE_0];
     const bool centered = c->GetKind_ConvNumScheme_Flow() == SPACE_CENTERED;
     if (c->GetMUSCL_Flow() && !centered) {

@@ -129,7 +129,8 @@ __global__ void k_bc_far_field(int nV, int Pd, FlowParams p, FarFieldInf inf, co
 #pragma unroll
     for (int k = 0; k < NV * NV; ++k) { vjac_i[k] = 0.0; vjac_j[k] = 0.0; }
     const double* g = grad_prim + (size_t)i * ngs * ND;
-    viscous_terms<ND, true>(p, Vd, Vj, g, g, vij, area, un, true, vflux, vjac_i, vjac_j);
+    // visc_bound_term = CAvgGrad_Flow(nDim, nVar, correct_gradient=false) (CDriver.cpp:1810)
+    viscous_terms<ND, true, true>(p, Vd, Vj, g, g, vij, area, un, false, vflux, vjac_i, vjac_j);
     // viscous_terms subtracts the viscous flux and its Jacobian from (flux, jac): exactly
     // LinSysRes.SubtractBlock / Jacobian.SubtractBlock2Diag of the reference.
 #pragma unroll
@@ -321,6 +322,55 @@ __global__ void k_pressure_force(int nV, int Pd, double p_inf, double factor, do
   for (int k = 0; k < 3; ++k) { out[(size_t)t * 6 + k] = f[k]; out[(size_t)t * 6 + 3 + k] = m[k]; }
 }
 
+// CFVMFlowSolverBase::Friction_Forces (CFVMFlowSolverBase.inl:2385-2720): tau from the laminar viscosity and the
+// primitive gradient at the wall point (CNumerics::ComputeStressTensor), force = tau.n * Area / AeroCoeffForceRef.
+template <int ND>
+__global__ void k_friction_force(int nV, int Pd, int ngs, double factor, double ref_len, double ox, double oy, double oz,
+                                 const int* __restrict__ vnode, const double* __restrict__ vnormal,
+                                 const double* __restrict__ coord, const double* __restrict__ V,
+                                 const double* __restrict__ grad_prim, double* __restrict__ out /*[nV][6]*/) {
+  using I = PrimIdx<ND>;
+  const int t = blockIdx.x * blockDim.x + threadIdx.x;
+  if (t >= nV) return;
+  const int i = vnode[t];
+  double f[3] = {0, 0, 0}, m[3] = {0, 0, 0};
+  if (i < Pd) {
+    const double mu = V[(size_t)i * I::NPRIM + I::MU];
+    const double* g = grad_prim + (size_t)i * ngs * ND;  // g[(1+a)*ND+b] = d v_a / d x_b
+    double n[ND], area = 0.0;
+#pragma unroll
+    for (int d = 0; d < ND; ++d) { n[d] = vnormal[(size_t)t * ND + d]; area += n[d] * n[d]; }
+    area = sqrt(area);
+#pragma unroll
+    for (int d = 0; d < ND; ++d) n[d] /= area;
+    double div = 0.0;
+#pragma unroll
+    for (int d = 0; d < ND; ++d) div += g[(1 + d) * ND + d];
+    const double pTerm = 2.0 / 3.0 * mu * div;
+    const double o[3] = {ox, oy, oz};
+    double md[3] = {0, 0, 0};
+#pragma unroll
+    for (int a = 0; a < ND; ++a) {
+      double te = 0.0;
+#pragma unroll
+      for (int b = 0; b < ND; ++b) {
+        double tau = mu * (g[(1 + b) * ND + a] + g[(1 + a) * ND + b]);
+        if (a == b) tau -= pTerm;
+        te += tau * n[b];
+      }
+      f[a] = te * area * factor;
+      md[a] = coord[(size_t)i * ND + a] - o[a];
+    }
+    if (ND == 3) {
+      m[0] = (f[2] * md[1] - f[1] * md[2]) / ref_len;
+      m[1] = (f[0] * md[2] - f[2] * md[0]) / ref_len;
+    }
+    m[2] = (f[1] * md[0] - f[0] * md[1]) / ref_len;
+  }
+#pragma unroll
+  for (int k = 0; k < 3; ++k) { out[(size_t)t * 6 + k] = f[k]; out[(size_t)t * 6 + 3 + k] = m[k]; }
+}
+
 // sequential-in-thread sum over vertices (vertex order == reference order), 6 threads
 __global__ void k_force_sum(int nV, const double* __restrict__ in, double* __restrict__ acc6) {
   const int k = threadIdx.x;
@@ -341,19 +391,31 @@ void flow_forces(su2b200_ctx* c, double* coeffs) {
   const double PI = 3.14159265358979323846;
   const double alpha = cfg.aoa_deg * PI / 180.0, beta = cfg.aos_deg * PI / 180.0;
   double CL = 0, CD = 0, CSF = 0, CF[3] = {0, 0, 0}, CM[3] = {0, 0, 0};
+  // pass 0: Pressure_Forces on every monitored marker; pass 1: Friction_Forces on monitored viscous walls
+  for (int pass = 0; pass < (cfg.viscous ? 2 : 1); ++pass)
   for (auto& m : g.markers) {
     if (!m.monitoring || m.nVertex == 0) continue;
+    if (pass == 1 && m.kind != SU2B200_HEAT_FLUX) continue;
     const size_t need = (size_t)m.nVertex * 6 + 8;
     if (s.red.n < need) s.red.alloc(need);
     double* buf = s.red.p;
     double* acc = s.red.p + (size_t)m.nVertex * 6;
     const int nb = nblk(m.nVertex, 128);
-    if (g.nDim == 2)
-      SU2B_LAUNCH(c, k_pressure_force<2>, nb, 128, m.nVertex, g.Pd, cfg.pressure_inf, factor, cfg.ref_length,
-                  cfg.ref_origin[0], cfg.ref_origin[1], cfg.ref_origin[2], m.node.p, m.normal.p, g.coord.p, s.V.p, buf);
-    else
-      SU2B_LAUNCH(c, k_pressure_force<3>, nb, 128, m.nVertex, g.Pd, cfg.pressure_inf, factor, cfg.ref_length,
-                  cfg.ref_origin[0], cfg.ref_origin[1], cfg.ref_origin[2], m.node.p, m.normal.p, g.coord.p, s.V.p, buf);
+    if (pass == 0) {
+      if (g.nDim == 2)
+        SU2B_LAUNCH(c, k_pressure_force<2>, nb, 128, m.nVertex, g.Pd, cfg.pressure_inf, factor, cfg.ref_length,
+                    cfg.ref_origin[0], cfg.ref_origin[1], cfg.ref_origin[2], m.node.p, m.normal.p, g.coord.p, s.V.p, buf);
+      else
+        SU2B_LAUNCH(c, k_pressure_force<3>, nb, 128, m.nVertex, g.Pd, cfg.pressure_inf, factor, cfg.ref_length,
+                    cfg.ref_origin[0], cfg.ref_origin[1], cfg.ref_origin[2], m.node.p, m.normal.p, g.coord.p, s.V.p, buf);
+    } else {
+      if (g.nDim == 2)
+        SU2B_LAUNCH(c, k_friction_force<2>, nb, 128, m.nVertex, g.Pd, s.nG, factor, cfg.ref_length, cfg.ref_origin[0],
+                    cfg.ref_origin[1], cfg.ref_origin[2], m.node.p, m.normal.p, g.coord.p, s.V.p, s.grad_prim.p, buf);
+      else
+        SU2B_LAUNCH(c, k_friction_force<3>, nb, 128, m.nVertex, g.Pd, s.nG, factor, cfg.ref_length, cfg.ref_origin[0],
+                    cfg.ref_origin[1], cfg.ref_origin[2], m.node.p, m.normal.p, g.coord.p, s.V.p, s.grad_prim.p, buf);
+    }
     SU2B_LAUNCH(c, k_force_sum, 1, 32, m.nVertex, buf, acc);
     SU2B_CUDA(cudaMemcpyAsync(s.h_red, acc, 6 * sizeof(double), cudaMemcpyDeviceToHost, c->stream));
     SU2B_CUDA(cudaStreamSynchronize(c->stream));

@@ -65,7 +65,9 @@ static void flow_preprocessing(su2b200_ctx* c, bool output, unsigned long* nonph
       }
     }
   } else {
-    const int nvars = output ? nd + 1 : nd + 2;
+    // nPrimVarGrad: nDim+1 for centred schemes (EulerNPrimVarGrad, CEulerVariable.cpp:31-42) and in the Output pass
+    // (CNSSolver.cpp:87-88), else nDim+2
+    const int nvars = (output || center) ? nd + 1 : nd + 2;
     if (!s.recon_aliases_prim && muscl && !center) {
       flow_gradient(c, 1, nvars);
       if (c->nranks > 1) halo_exchange(c, s.grad_recon.p, s.nG * nd);

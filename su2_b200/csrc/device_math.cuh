@@ -271,7 +271,10 @@ __device__ __forceinline__ void scalar_dissipation_jacobian(const double* V, dou
 // CCompressibleViscousFlux (ideal gas, :253-298). Vi/Vj are the un-reconstructed primitives (all ND+9),
 // gi/gj the primitive gradients [(ND+1)][ND] of (T, v). Subtracts the viscous flux from `flux` and
 // updates jac_i/jac_j. `correct` = edge-correction of the mean gradient (finest grid).
-template <int ND, bool IMPLICIT>
+// LEGACY = the boundary functor CAvgGrad_Flow (flow_diffusion.cpp:368-532): same flux, but its heat-flux Jacobian
+// uses cp/R * (k/cp + mu_t/Pr_t) (SetHeatFluxJacobian :489-532), which differs from the SIMD form when the mean cp
+// is not the gas cp (far-field state carries cp = k = 0, CEulerSolver.cpp:4990-4993).
+template <int ND, bool IMPLICIT, bool LEGACY = false>
 __device__ __forceinline__ void viscous_terms(const FlowParams& p, const double* Vi, const double* Vj,
                                               const double* gi, const double* gj, const double* vec_ij,
                                               double area, const double* un, bool correct,
@@ -356,7 +359,8 @@ __device__ __forceinline__ void viscous_terms(const FlowParams& p, const double*
   const double vel2 = 0.5 * dotN<ND>(&avgV[I::VEL], &avgV[I::VEL]);
   const double phi = (p.gamma - 1) / avgV[I::RHO];
   const double RdTdrho = phi * vel2 - avgV[I::P] / (avgV[I::RHO] * avgV[I::RHO]);
-  const double condOnRd = cond / (p.R * dist);
+  const double condOnRd = LEGACY ? (p.gamma / (p.gamma - 1)) * (avgV[I::K] / avgV[I::CP] + avgV[I::MUT] / p.prandtl_turb) / dist
+                                 : cond / (p.R * dist);
   double contraction = 0.0;
 #pragma unroll
   for (int d = 0; d < ND; ++d) contraction += dtau[d * NV + 0] * avgV[I::VEL + d];

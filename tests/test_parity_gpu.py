@@ -65,7 +65,8 @@ def test_history_tracks_reference(case):
     nv = s.nVar
     for i, r in enumerate(reps):
         ref_rms = hist[i, :nv]
-        ok = np.abs(r["rms_flow"] - ref_rms) <= 1e-6 * np.abs(ref_rms) + 1e-15
+        # components that are identically zero in exact arithmetic (e.g. spanwise momentum) are round-off noise
+        ok = np.abs(r["rms_flow"] - ref_rms) <= 1e-6 * np.abs(ref_rms) + 1e-12 * np.max(np.abs(ref_rms))
         assert ok.all(), (i, r["rms_flow"], ref_rms)
         assert abs(r["CL"] - hist[i, 6]) <= 1e-6 * max(1e-3, abs(hist[i, 6])), (i, r["CL"], hist[i, 6])
         assert abs(r["CD"] - hist[i, 7]) <= 1e-6 * max(1e-3, abs(hist[i, 7])), (i, r["CD"], hist[i, 7])
