@@ -142,6 +142,34 @@ int su2b200_p2p_upload(su2b200_ctx* ctx, int nNeighborRanks, const int* neighbor
                        const int* nPoint_P2PSend /*[n+1] cumulative*/, const unsigned long* Local_Point_P2PSend,
                        const int* nPoint_P2PRecv /*[n+1] cumulative*/, const unsigned long* Local_Point_P2PRecv);
 
+/* ---- host-side geometry preprocessing: the part of CGeometry/CPhysicalGeometry the path consumes (host C++, no GPU needed) ----
+ * Produces exactly the arrays of su2b200_geometry_desc / su2b200_marker_upload / su2b200_p2p_upload. */
+typedef struct su2b200_mesh su2b200_mesh;
+/* MESH_FORMAT= BOX / RECTANGLE (CBoxMeshReaderFVM.cpp:31-330, CRectangularMeshReaderFVM.cpp): n points per direction,
+ * markers x_minus, x_plus, y_minus, y_plus[, z_minus, z_plus]; the local part of `rank` in a slab decomposition along the
+ * last axis (owned points first, one halo plane per neighbour, halo tables as CGeometry::PreprocessP2PComms builds them).
+ * tets != 0 splits every hexahedron into 6 tetrahedra (quadrilateral into 2 triangles). */
+int su2b200_mesh_create_box(int nDim, const unsigned long n[3], const double length[3], const double offset[3],
+                            int rank, int nranks, int tets, su2b200_mesh** out);
+/* MESH_FORMAT= SU2 (CSU2ASCIIMeshReaderBase.cpp): NDIME / NELEM / NPOIN / NMARK blocks, VTK element ids */
+int su2b200_mesh_read_su2(const char* path, su2b200_mesh** out);
+int su2b200_mesh_destroy(su2b200_mesh* mesh);
+/* MARKER_EULER / MARKER_FAR / MARKER_SYM / MARKER_HEATFLUX + MARKER_MONITORING of the cfg file */
+int su2b200_mesh_set_marker(su2b200_mesh* mesh, const char* tag, int kindBC, int monitoring, double heat_flux);
+/* SetRCM_Ordering (CPhysicalGeometry.cpp:4478, if rcm != 0), SetEdges (CGeometry.cpp:1263), SetControlVolume
+ * (CPhysicalGeometry.cpp:7059), SetBoundControlVolume (:7212), FindNormal_Neighbor (:8036), ComputeModifiedSymmetryNormals
+ * (CGeometry.cpp:2469), ComputeWall_Distance, GetSparsePattern (:3702), GetEdgeToSparsePatternMap (:3720), GetEdgeColoring (:3737) */
+int su2b200_mesh_preprocess(su2b200_mesh* mesh, int rcm);
+int su2b200_mesh_sizes(su2b200_mesh* mesh, int* nDim, unsigned long* nPoint, unsigned long* nPointDomain,
+                       unsigned long* nEdge, unsigned long* nElem, unsigned long* nnz, int* nMarker);
+/* read-only view of a named array ("coord", "volume", "edge_normal", "edge_node0", "row_ptr", "marker0_normal", ...);
+ * dtype: 0 = double, 1 = unsigned long, 2 = unsigned short, 3 = unsigned char, 4 = int */
+int su2b200_mesh_array(su2b200_mesh* mesh, const char* name, const void** data, unsigned long* count, int* dtype);
+int su2b200_mesh_marker_info(su2b200_mesh* mesh, int iMarker, char tag[64], int* kindBC, int* monitoring,
+                             unsigned long* nVertex, unsigned long* nElemBound);
+/* geometry_upload + marker_upload for every marker + p2p_upload */
+int su2b200_mesh_upload(su2b200_ctx* ctx, su2b200_mesh* mesh);
+
 /* ---- configuration: the CConfig getters the hot path reads, as a POD ------------------ */
 
 typedef struct {
@@ -292,6 +320,12 @@ int su2b200_timer_start(su2b200_ctx* ctx);
 int su2b200_timer_stop(su2b200_ctx* ctx, float* ms);
 /* kernels launched by this context since creation (bench.py's gpu_launches) */
 unsigned long su2b200_launch_count(su2b200_ctx* ctx);
+/* per-category device time of the calls made while enabled (CUDA events on the compute stream): bench.py's kernel shares.
+ * ms/calls have su2b200_profile_ncat() entries, named by su2b200_profile_name(). Keep it off inside timed regions. */
+int su2b200_profile_enable(su2b200_ctx* ctx, int on);
+int su2b200_profile_ncat(void);
+const char* su2b200_profile_name(int cat);
+int su2b200_profile_report(su2b200_ctx* ctx, double* ms, unsigned long* calls);
 /* micro-benchmarks of the two roofline kernels on the resident state: average ms over `reps` launches */
 int su2b200_bench_edge_kernel(su2b200_ctx* ctx, int reps, float* ms_avg);
 int su2b200_bench_spmv(su2b200_ctx* ctx, int which, int reps, float* ms_avg);

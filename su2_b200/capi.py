@@ -98,6 +98,10 @@ EXPORTED_SYMBOLS = [
     "su2b200_vector_dot", "su2b200_comm_unique_id", "su2b200_comm_init", "su2b200_halo_exchange",
     "su2b200_timer_start", "su2b200_timer_stop", "su2b200_launch_count", "su2b200_bench_edge_kernel",
     "su2b200_bench_spmv", "su2b200_struct_sizes",
+    "su2b200_mesh_create_box", "su2b200_mesh_read_su2", "su2b200_mesh_destroy", "su2b200_mesh_set_marker",
+    "su2b200_mesh_preprocess", "su2b200_mesh_sizes", "su2b200_mesh_array", "su2b200_mesh_marker_info",
+    "su2b200_mesh_upload", "su2b200_profile_enable", "su2b200_profile_ncat", "su2b200_profile_name",
+    "su2b200_profile_report",
 ]
 
 _lib = None
@@ -119,6 +123,7 @@ def load():
     lib.su2b200_last_error.restype = C.c_char_p
     lib.su2b200_array_size.restype = C.c_long
     lib.su2b200_launch_count.restype = C.c_ulong
+    lib.su2b200_profile_name.restype = C.c_char_p
     g = C.c_int()
     f = C.c_int()
     r = C.c_int()

@@ -231,6 +231,7 @@ __global__ void k_bc_heatflux_wall(int nV, int Pd, double wall_heat_flux, const 
 }
 
 void flow_bc_far_field(su2b200_ctx* c, int iMarker) {
+  ProfScope prof_(c, PROF_BC);
   auto& g = c->geo;
   auto& s = c->fs;
   auto& m = g.markers.at(iMarker);
@@ -260,6 +261,7 @@ void flow_bc_far_field(su2b200_ctx* c, int iMarker) {
 }
 
 void flow_bc_sym_plane(su2b200_ctx* c, int iMarker) {
+  ProfScope prof_(c, PROF_BC);
   auto& g = c->geo;
   auto& s = c->fs;
   auto& m = g.markers.at(iMarker);
@@ -272,6 +274,7 @@ void flow_bc_sym_plane(su2b200_ctx* c, int iMarker) {
 }
 
 void flow_bc_heatflux_wall(su2b200_ctx* c, int iMarker) {
+  ProfScope prof_(c, PROF_BC);
   auto& g = c->geo;
   auto& s = c->fs;
   auto& m = g.markers.at(iMarker);
@@ -381,6 +384,7 @@ __global__ void k_force_sum(int nV, const double* __restrict__ in, double* __res
 }
 
 void flow_forces(su2b200_ctx* c, double* coeffs) {
+  ProfScope prof_(c, PROF_FORCES);
   auto& g = c->geo;
   auto& s = c->fs;
   const auto& cfg = c->cfg;

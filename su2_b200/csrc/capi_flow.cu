@@ -453,6 +453,37 @@ int su2b200_timer_stop(su2b200_ctx* c, float* ms) {
 }
 unsigned long su2b200_launch_count(su2b200_ctx* c) { return c ? c->launches : 0; }
 
+int su2b200_profile_enable(su2b200_ctx* c, int on) {
+  API_BEGIN
+  if (!c) throw Error("null context");
+  SU2B_CUDA(cudaStreamSynchronize(c->stream));
+  for (auto& r : c->prof.recs) { c->prof.pool.push_back(r.a); c->prof.pool.push_back(r.b); }
+  c->prof.recs.clear();
+  c->prof.on = on != 0;
+  API_END
+}
+int su2b200_profile_ncat(void) { return PROF_NCAT; }
+const char* su2b200_profile_name(int cat) {
+  static const char* names[PROF_NCAT] = {"primitives", "gradient", "limiter", "time_step", "jst_preprocess", "edge_flux",
+                                         "point_sum", "boundary", "prepare_implicit", "prec_build", "prec_apply", "spmv",
+                                         "dot", "vector_ops", "update", "forces", "turb_edge", "turb_source",
+                                         "turb_other", "halo"};
+  return (cat >= 0 && cat < PROF_NCAT) ? names[cat] : "";
+}
+int su2b200_profile_report(su2b200_ctx* c, double* ms, unsigned long* calls) {
+  API_BEGIN
+  if (!c) throw Error("null context");
+  SU2B_CUDA(cudaStreamSynchronize(c->stream));
+  for (int k = 0; k < PROF_NCAT; ++k) { if (ms) ms[k] = 0.0; if (calls) calls[k] = 0; }
+  for (auto& r : c->prof.recs) {
+    float t = 0;
+    SU2B_CUDA(cudaEventElapsedTime(&t, r.a, r.b));
+    if (ms) ms[r.cat] += t;
+    if (calls) calls[r.cat]++;
+  }
+  API_END
+}
+
 int su2b200_bench_edge_kernel(su2b200_ctx* c, int reps, float* ms_avg) {
   API_BEGIN
   require_flow(c);

@@ -364,11 +364,13 @@ void flow_edge_residual(su2b200_ctx* c, unsigned long* nonphysical_edges) {
     }
   } else {
     if (g.nDim == 2) {
-      launch_edge<2>(c, a, p, g.E, false);
+      { ProfScope prof_(c, PROF_EDGE); launch_edge<2>(c, a, p, g.E, false); }
+      ProfScope prof2_(c, PROF_POINT_SUM);
       SU2B_LAUNCH(c, k_point_sum<4>, nblk(g.P, 128), 128, g.P, g.E, g.nbr_ptr.p, g.gat_edge.p, g.gat_blk.p,
                   g.dia_ptr.p, s.edge_flux.p, ls.A.p, s.res.p);
     } else {
-      launch_edge<3>(c, a, p, g.E, false);
+      { ProfScope prof_(c, PROF_EDGE); launch_edge<3>(c, a, p, g.E, false); }
+      ProfScope prof2_(c, PROF_POINT_SUM);
       SU2B_LAUNCH(c, k_point_sum<5>, nblk(g.P, 128), 128, g.P, g.E, g.nbr_ptr.p, g.gat_edge.p, g.gat_blk.p,
                   g.dia_ptr.p, s.edge_flux.p, ls.A.p, s.res.p);
     }

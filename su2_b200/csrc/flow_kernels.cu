@@ -683,6 +683,7 @@ static PrimParams make_prim_params(const su2b200_flow_config& c) {
 }
 
 void flow_primitives(su2b200_ctx* c) {
+  ProfScope prof_(c, PROF_PRIMITIVES);
   auto& g = c->geo;
   auto& s = c->fs;
   const PrimParams pp = make_prim_params(c->cfg);
@@ -720,6 +721,7 @@ static void gradient_impl(su2b200_ctx* c, int method, double* grad, int ngs) {
 // reconstruction != 0 -> Gradient_Reconstruction with NUM_METHOD_GRAD_RECON, else Gradient_Primitive.
 // nvars: nDim+2 (all reconstructed variables) or nDim+1 (Output pass of CNSSolver::Preprocessing).
 void flow_gradient(su2b200_ctx* c, int reconstruction, int nvars) {
+  ProfScope prof_(c, PROF_GRADIENT);
   auto& s = c->fs;
   const int nd = c->geo.nDim;
   const int method = reconstruction ? c->cfg.grad_method_recon : c->cfg.grad_method;
@@ -733,6 +735,7 @@ void flow_gradient(su2b200_ctx* c, int reconstruction, int nvars) {
 }
 
 void flow_limiter(su2b200_ctx* c) {
+  ProfScope prof_(c, PROF_LIMITER);
   auto& g = c->geo;
   auto& s = c->fs;
   const double macheps = 2.220446049250313e-16;
@@ -769,6 +772,7 @@ static void spectral_radius_impl(su2b200_ctx* c, int viscous, double* lam_inv, d
 }
 
 void flow_time_step(su2b200_ctx* c) {
+  ProfScope prof_(c, PROF_TIMESTEP);
   auto& g = c->geo;
   auto& s = c->fs;
   const int visc = c->cfg.viscous;
@@ -786,6 +790,7 @@ void flow_time_step(su2b200_ctx* c) {
 }
 
 void flow_jst_preprocess(su2b200_ctx* c) {
+  ProfScope prof_(c, PROF_JST_PRE);
   auto& g = c->geo;
   auto& s = c->fs;
   if (g.nDim == 2) {
@@ -800,6 +805,7 @@ void flow_jst_preprocess(su2b200_ctx* c) {
 }
 
 void flow_vorticity_strain(su2b200_ctx* c) {
+  ProfScope prof_(c, PROF_GRADIENT);
   auto& g = c->geo;
   auto& s = c->fs;
   if (g.nDim == 2) LAUNCH(c, k_vorticity_strain<2>, nblk(g.P, 256), 256, g.P, s.nG, s.grad_prim.p, s.vorticity.p, s.strain_mag.p);
@@ -838,17 +844,20 @@ static void prepare_implicit_impl(su2b200_ctx* c, LinSys& ls, const double* dt, 
 }
 
 void flow_prepare_implicit(su2b200_ctx* c, double* rms, double* mx, unsigned long* idx) {
+  ProfScope prof_(c, PROF_PREPARE);
   auto& s = c->fs;
   if (c->geo.nDim == 2) prepare_implicit_impl<4>(c, c->sys[0], s.dt.p, s.res.p, s.sol.p, rms, mx, idx);
   else prepare_implicit_impl<5>(c, c->sys[0], s.dt.p, s.res.p, s.sol.p, rms, mx, idx);
 }
 
 void turb_prepare_implicit_generic(su2b200_ctx* c, double* rms, double* mx, unsigned long* idx) {
+  ProfScope prof_(c, PROF_PREPARE);
   auto& s = c->fs;
   prepare_implicit_impl<1>(c, c->sys[1], s.turb_dt.p, s.turb_res.p, s.turb_sol.p, rms, mx, idx);
 }
 
 void flow_complete_implicit(su2b200_ctx* c) {
+  ProfScope prof_(c, PROF_UPDATE);
   auto& g = c->geo;
   auto& s = c->fs;
   if (g.nDim == 2) LAUNCH(c, k_complete_implicit<4>, nblk(g.Pd, 256), 256, g.Pd, c->cfg.max_update_flow, s.sol.p, s.U_old.p, s.U.p, s.under_relax.p);

@@ -168,6 +168,23 @@ struct FlowState {
   bool recon_aliases_prim = false;           // Gradient_Reconstruction is Gradient_Primitive
 };
 
+// ---- optional per-category device timing (bench.py's kernel shares; off in timed regions) ------------------
+enum ProfCat { PROF_PRIMITIVES = 0, PROF_GRADIENT, PROF_LIMITER, PROF_TIMESTEP, PROF_JST_PRE, PROF_EDGE, PROF_POINT_SUM,
+               PROF_BC, PROF_PREPARE, PROF_PREC_BUILD, PROF_PREC_APPLY, PROF_SPMV, PROF_DOT, PROF_VECOPS, PROF_UPDATE,
+               PROF_FORCES, PROF_TURB_EDGE, PROF_TURB_SOURCE, PROF_TURB_OTHER, PROF_HALO, PROF_NCAT };
+struct Profiler {
+  bool on = false;
+  struct Rec { int cat; cudaEvent_t a, b; };
+  std::vector<Rec> recs;
+  std::vector<cudaEvent_t> pool;
+  cudaEvent_t get() {
+    if (!pool.empty()) { cudaEvent_t e = pool.back(); pool.pop_back(); return e; }
+    cudaEvent_t e;
+    cudaEventCreate(&e);
+    return e;
+  }
+};
+
 }  // namespace su2b200
 
 struct su2b200_ctx {
@@ -191,4 +208,20 @@ struct su2b200_ctx {
   unsigned long lin_iters[2] = {0, 0};
   double lin_res[2] = {0, 0};
   double min_dt = 0, max_dt = 0;
+  su2b200::Profiler prof;
 };
+
+namespace su2b200 {
+// RAII scope: records two events on the compute stream around a category when profiling is enabled
+struct ProfScope {
+  su2b200_ctx* c;
+  cudaEvent_t a = nullptr;
+  int cat;
+  ProfScope(su2b200_ctx* ctx, int category) : c(ctx), cat(category) {
+    if (c->prof.on) { a = c->prof.get(); cudaEventRecord(a, c->stream); }
+  }
+  ~ProfScope() {
+    if (a) { cudaEvent_t b = c->prof.get(); cudaEventRecord(b, c->stream); c->prof.recs.push_back({cat, a, b}); }
+  }
+};
+}  // namespace su2b200

@@ -52,16 +52,20 @@ __global__ void k_set_scaled(size_t n, double alpha, const double* __restrict__ 
 static inline int vec_grid(size_t n) { return (int)std::min<size_t>((n + 255) / 256, 148 * 8); }
 
 void vec_axpy(su2b200_ctx* c, size_t n, double alpha, const double* x, double* y) {
+  ProfScope prof_(c, PROF_VECOPS);
   SU2B_LAUNCH(c, k_axpy, vec_grid(n), 256, n, alpha, x, y);
 }
 void vec_axpby(su2b200_ctx* c, size_t n, double alpha, const double* x, double beta, double* y) {
+  ProfScope prof_(c, PROF_VECOPS);
   SU2B_LAUNCH(c, k_axpby, vec_grid(n), 256, n, alpha, x, beta, y);
 }
 void vec_scale(su2b200_ctx* c, size_t n, double alpha, double* x) { SU2B_LAUNCH(c, k_scale, vec_grid(n), 256, n, alpha, x); }
 void vec_set_scaled(su2b200_ctx* c, size_t n, double alpha, const double* x, double* y) {
+  ProfScope prof_(c, PROF_VECOPS);
   SU2B_LAUNCH(c, k_set_scaled, vec_grid(n), 256, n, alpha, x, y);
 }
 void vec_copy(su2b200_ctx* c, size_t n, const double* x, double* y) {
+  ProfScope prof_(c, PROF_VECOPS);
   SU2B_CUDA(cudaMemcpyAsync(y, x, n * sizeof(double), cudaMemcpyDeviceToDevice, c->stream));
 }
 
@@ -105,6 +109,7 @@ static void ensure_scalars(LinSys& ls) {
 }
 
 double vec_dot(su2b200_ctx* c, LinSys& ls, const double* a, const double* b) {
+  ProfScope prof_(c, PROF_DOT);
   ensure_scalars(ls);
   const size_t n = (size_t)ls.Pd * ls.nVar;
   const int nb = (int)std::min<size_t>((n + 255) / 256, DOT_BLOCKS);
@@ -172,6 +177,7 @@ __global__ void __launch_bounds__(256) k_spmv_scalar(int Pd, const int* __restri
 }
 
 void linsys_spmv(su2b200_ctx* c, LinSys& ls, const double* x, double* y) {
+  ProfScope prof_(c, PROF_SPMV);
   const long threads = (long)ls.Pd * 32;
   switch (ls.nVar) {
     case 1: SU2B_LAUNCH(c, k_spmv_scalar, nblk((long)ls.Pd * 8, 256), 256, ls.Pd, ls.row_ptr, ls.col_ind, ls.A.p, x, y); break;

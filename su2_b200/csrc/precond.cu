@@ -454,6 +454,7 @@ void linsys_apply_lusgs(su2b200_ctx* c, LinSys& ls, const double* b, double* x) 
 }
 
 void linsys_build_prec(su2b200_ctx* c, LinSys& ls, int prec) {
+  ProfScope prof_(c, PROF_PREC_BUILD);
   switch (prec) {
     case SU2B200_PREC_JACOBI: linsys_build_jacobi(c, ls); break;
     case SU2B200_PREC_ILU: linsys_build_ilu(c, ls); break;
@@ -462,6 +463,7 @@ void linsys_build_prec(su2b200_ctx* c, LinSys& ls, int prec) {
   }
 }
 void linsys_apply_prec(su2b200_ctx* c, LinSys& ls, int prec, const double* x, double* y) {
+  ProfScope prof_(c, PROF_PREC_APPLY);
   switch (prec) {
     case SU2B200_PREC_JACOBI: linsys_apply_jacobi(c, ls, x, y); break;
     case SU2B200_PREC_ILU: linsys_apply_ilu(c, ls, x, y); break;

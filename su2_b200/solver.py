@@ -128,6 +128,28 @@ class FlowSolver:
             raise ValueError(f"{name}: expected {n} values, got {v.size}")
         check(self.lib.su2b200_array_upload(self.ctx, wid, ptr_d(v)))
 
+    def download_into(self, name, host):
+        """D2H copy of a named device array into a caller-owned (ideally pinned) float64 buffer."""
+        wid = capi.ARR[name]
+        assert host.dtype == np.float64 and host.size == self.lib.su2b200_array_size(self.ctx, wid)
+        check(self.lib.su2b200_array_download(self.ctx, wid, ptr_d(host)))
+
+    def upload_from(self, name, host):
+        wid = capi.ARR[name]
+        assert host.dtype == np.float64 and host.size == self.lib.su2b200_array_size(self.ctx, wid)
+        check(self.lib.su2b200_array_upload(self.ctx, wid, ptr_d(host)))
+
+    # ---- communication (one context == one rank == one GPU) -----------------------------------------------
+    def comm_unique_id(self):
+        buf = (C.c_ubyte * 128)()
+        check(self.lib.su2b200_comm_unique_id(buf))
+        return np.frombuffer(buf, dtype=np.uint8).copy()
+
+    def comm_init(self, rank, size, unique_id):
+        uid = np.ascontiguousarray(unique_id, dtype=np.uint8)
+        assert uid.size == 128
+        check(self.lib.su2b200_comm_init(self.ctx, int(rank), int(size), uid.ctypes.data_as(C.POINTER(C.c_ubyte))))
+
     def edge_counter(self):
         out = np.empty(self.nEdge, dtype=np.int8)
         check(self.lib.su2b200_edge_counter_download(self.ctx, out.ctypes.data_as(C.POINTER(C.c_byte))))
@@ -243,6 +265,16 @@ class FlowSolver:
 
     def launch_count(self):
         return int(self.lib.su2b200_launch_count(self.ctx))
+
+    def profile_enable(self, on=True):
+        check(self.lib.su2b200_profile_enable(self.ctx, int(bool(on))))
+
+    def profile_report(self):
+        n = self.lib.su2b200_profile_ncat()
+        ms = (C.c_double * n)()
+        calls = (C.c_ulong * n)()
+        check(self.lib.su2b200_profile_report(self.ctx, ms, calls))
+        return {self.lib.su2b200_profile_name(k).decode(): (ms[k], calls[k]) for k in range(n) if calls[k]}
 
     def bench_edge_kernel(self, reps=10):
         ms = C.c_float()
