@@ -95,4 +95,10 @@ def config_from_dump(d):
         turb_linear_tol=d["cfg_linear_tol"], turb_linear_iter=int(d["cfg_linear_iter"]),
         aoa_deg=d["cfg_aoa"], aos_deg=d["cfg_aos"], ref_area=d["cfg_ref_area"], ref_length=d["cfg_ref_length"],
         ref_origin=list(d["cfg_ref_origin"]))
+    if kw["rans_sa"]:
+        # free-stream eddy viscosity of the CTurbSASolver constructor (CTurbSASolver.cpp:100-134)
+        t = kw["temperature_inf"]
+        mu = kw["mu_ref"] * (t / kw["mu_temperature_ref"]) ** 1.5 * (kw["mu_temperature_ref"] + kw["mu_sutherland"]) / (t + kw["mu_sutherland"])
+        chi = kw["nu_tilde_inf"] / (mu / kw["density_inf"])
+        kw["eddy_visc_inf"] = kw["density_inf"] * chi ** 3 / (chi ** 3 + 7.1 ** 3) * kw["nu_tilde_inf"]
     return kw

@@ -734,6 +734,48 @@ void flow_gradient(su2b200_ctx* c, int reconstruction, int nvars) {
   }
 }
 
+// scalar variant of the symmetry correction (idxVel = -1: only n.grad(phi) = 0), one launch per sym marker
+template <int ND>
+__global__ void k_grad_sym_scalar(int nV, const int* __restrict__ vnode, const double* __restrict__ unit,
+                                  double* __restrict__ grad) {
+  const int t = blockIdx.x * blockDim.x + threadIdx.x;
+  if (t >= nV) return;
+  const int i = vnode[t];
+  double ng = 0.0;
+#pragma unroll
+  for (int d = 0; d < ND; ++d) ng += unit[(size_t)t * ND + d] * grad[(size_t)i * ND + d];
+#pragma unroll
+  for (int d = 0; d < ND; ++d) grad[(size_t)i * ND + d] -= ng * unit[(size_t)t * ND + d];
+}
+
+// CScalarSolver::SetSolution_Gradient_GG / _LS (CScalarSolver.inl:88-127 via CSolver::SetSolution_Gradient_*):
+// gradient of a one-variable field [P] -> [P][ND], idxVel = -1.
+template <int ND>
+static void scalar_gradient_impl(su2b200_ctx* c, int method, const double* field, double* grad) {
+  auto& g = c->geo;
+  if (method == SU2B200_GRAD_GREEN_GAUSS) {
+    LAUNCH(c, (k_grad_gg<ND, 1>), nblk(g.Pd, 128), 128, g.Pd, 1, 1, g.nbr_ptr.p, g.nbr_pt.p, g.nbr_edge.p,
+           g.edge_normal.p, g.E, g.volume.p, field, grad);
+    for (auto& m : g.markers) {
+      if (m.kind == SU2B200_SEND_RECEIVE || m.nVertex == 0) continue;
+      LAUNCH(c, (k_grad_gg_bnd<ND, 1>), nblk(m.nVertex, 128), 128, m.nVertex, g.Pd, 1, 1, m.node.p, m.normal.p,
+             g.volume.p, field, grad);
+    }
+  } else {
+    const int weighted = (method == SU2B200_GRAD_WEIGHTED_LEAST_SQUARES);
+    LAUNCH(c, (k_grad_ls<ND, 1>), nblk(g.Pd, 128), 128, g.Pd, 1, 1, weighted, g.nbr_ptr.p, g.nbr_pt.p, g.coord.p, field,
+           grad);
+  }
+  for (auto& m : g.markers)
+    if ((m.kind == SU2B200_SYMMETRY_PLANE || m.kind == SU2B200_EULER_WALL) && m.nVertex > 0)
+      LAUNCH(c, k_grad_sym_scalar<ND>, nblk(m.nVertex, 128), 128, m.nVertex, m.node.p, m.unit_sym.p, grad);
+}
+void scalar_gradient(su2b200_ctx* c, int method, const double* field, double* grad) {
+  ProfScope prof_(c, PROF_GRADIENT);
+  if (c->geo.nDim == 2) scalar_gradient_impl<2>(c, method, field, grad);
+  else scalar_gradient_impl<3>(c, method, field, grad);
+}
+
 void flow_limiter(su2b200_ctx* c) {
   ProfScope prof_(c, PROF_LIMITER);
   auto& g = c->geo;

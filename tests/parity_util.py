@@ -120,3 +120,41 @@ def run_first_iteration(s, gold, it=0, report=None, check=None):
     cmp("under_relax", s.get("UNDER_RELAX"), pre + "under_relax")
     s.Preprocessing(True)
     return rms
+
+
+def run_turb_iteration(s, gold, it=0, report=None):
+    """CSingleGridIntegration::SingleGrid_Iteration(TURB_SOL) stage by stage, after run_first_iteration(s, gold, it)."""
+    pre = "it%d_turb_" % it
+    nd, P = s.nDim, s.nPoint
+
+    def cmp(name, got, key):
+        if key not in gold:
+            return
+        e = relerr(got, gold[key])
+        if report is not None:
+            report[name] = e
+            if "_keep" in report:
+                report["_keep"][name] = (np.array(got, copy=True), np.array(gold[key], copy=True))
+
+    s.Turb_Preprocessing()
+
+
+    if pre + "pre_gradient" in gold:
+        g = gold[pre + "pre_gradient"].reshape(P, nd)[:s.nPointDomain]
+        e = relerr(s.get("TURB_GRADIENT").reshape(P, nd)[:s.nPointDomain], g)
+        if report is not None:
+            report["turb_gradient"] = e
+    s.set("TURB_SOLUTION_OLD", s.get("TURB_SOLUTION"))  # Set_OldSolution
+    s.Turb_SetTime_Step()
+    cmp("turb_delta_time", s.get("TURB_DELTA_TIME"), pre + "delta_time")
+    s.Turb_Space_Integration()
+    cmp("turb_bc_residual", s.get("TURB_LINSYSRES"), pre + "bc_linsysres")
+    cmp("turb_bc_jacobian", s.get("TURB_JACOBIAN"), pre + "bc_jacobian")
+    s.Turb_PrepareImplicitIteration()
+    iters, res = s.Turb_Solve()
+    cmp("turb_linsyssol", s.get("TURB_LINSYSSOL"), pre + "linsyssol")
+    s.Turb_CompleteImplicitIteration()
+    s.Turb_Postprocessing()
+    cmp("turb_post_solution", s.get("TURB_SOLUTION"), pre + "post_solution")
+    cmp("turb_post_mut", s.get("EDDY_VISC"), pre + "post_mut")
+    return iters
