@@ -329,6 +329,7 @@ int su2b200_profile_report(su2b200_ctx* ctx, double* ms, unsigned long* calls);
 /* micro-benchmarks of the two roofline kernels on the resident state: average ms over `reps` launches */
 int su2b200_bench_edge_kernel(su2b200_ctx* ctx, int reps, float* ms_avg);
 int su2b200_bench_spmv(su2b200_ctx* ctx, int which, int reps, float* ms_avg);
+int su2b200_bench_prec(su2b200_ctx* ctx, int which, int prec, int reps, float* ms_build, float* ms_apply);
 
 #ifdef __cplusplus
 }

@@ -385,6 +385,7 @@ int su2b200_linsys_build_preconditioner(su2b200_ctx* c, int which, int prec) {
   API_BEGIN
   auto& ls = get_sys(c, which);
   linsys_build_prec(c, ls, prec);
+  linsys_check_sweeps(c, ls);
   SU2B_CUDA(cudaStreamSynchronize(c->stream));
   API_END
 }
@@ -398,6 +399,7 @@ int su2b200_linsys_apply_preconditioner(su2b200_ctx* c, int which, int prec, con
   SU2B_CUDA(cudaMemcpyAsync(dx, x, n * sizeof(double), cudaMemcpyHostToDevice, c->stream));
   SU2B_CUDA(cudaMemsetAsync(dy, 0, n * sizeof(double), c->stream));
   linsys_apply_prec(c, ls, prec, dx, dy);
+  linsys_check_sweeps(c, ls);
   SU2B_CUDA(cudaMemcpyAsync(y, dy, n * sizeof(double), cudaMemcpyDeviceToHost, c->stream));
   SU2B_CUDA(cudaStreamSynchronize(c->stream));
   API_END
@@ -505,6 +507,34 @@ int su2b200_bench_spmv(su2b200_ctx* c, int which, int reps, float* ms_avg) {
   float ms = 0;
   SU2B_CUDA(cudaEventElapsedTime(&ms, c->ev0, c->ev1));
   *ms_avg = ms / reps;
+  API_END
+}
+
+// preconditioner micro-benchmark on the resident matrix of system `which`: average ms of `reps` builds and applies
+int su2b200_bench_prec(su2b200_ctx* c, int which, int prec, int reps, float* ms_build, float* ms_apply) {
+  API_BEGIN
+  auto& ls = get_sys(c, which);
+  double* dx = ls.vec(0).p;
+  double* dy = ls.vec(1).p;
+  const int nr = c->nranks;
+  c->nranks = 1;  // kernels only
+  linsys_build_prec(c, ls, prec);  // warm-up (level schedule, allocations)
+  linsys_apply_prec(c, ls, prec, dx, dy);
+  float ms = 0;
+  SU2B_CUDA(cudaEventRecord(c->ev0, c->stream));
+  for (int r = 0; r < reps; ++r) linsys_build_prec(c, ls, prec);
+  SU2B_CUDA(cudaEventRecord(c->ev1, c->stream));
+  SU2B_CUDA(cudaEventSynchronize(c->ev1));
+  SU2B_CUDA(cudaEventElapsedTime(&ms, c->ev0, c->ev1));
+  if (ms_build) *ms_build = ms / reps;
+  SU2B_CUDA(cudaEventRecord(c->ev0, c->stream));
+  for (int r = 0; r < reps; ++r) linsys_apply_prec(c, ls, prec, dx, dy);
+  SU2B_CUDA(cudaEventRecord(c->ev1, c->stream));
+  SU2B_CUDA(cudaEventSynchronize(c->ev1));
+  SU2B_CUDA(cudaEventElapsedTime(&ms, c->ev0, c->ev1));
+  if (ms_apply) *ms_apply = ms / reps;
+  c->nranks = nr;
+  linsys_check_sweeps(c, ls);
   API_END
 }
 

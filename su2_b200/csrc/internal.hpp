@@ -133,6 +133,18 @@ struct LinSys {
   std::vector<int> lvl_ptr_lower, lvl_ptr_upper;  // host offsets into the row lists
   dvec<int> lvl_rows_lower, lvl_rows_upper;
   int nlev_lower = 0, nlev_upper = 0;
+  // single-launch dependency-driven sweeps (precond.cu): rows in level order, padded per level to the group size;
+  // ready[i] == epoch marks row i as finished in the current sweep; ctrl = {ticket, abort}
+  dvec<int> sweep_rows_lower, sweep_rows_upper;
+  int sweep_n_lower = 0, sweep_n_upper = 0;
+  dvec<int> sweep_ready, sweep_ctrl;
+  int sweep_epoch = 0;
+  int* h_sweep_ctrl = nullptr;       // pinned
+  int sweep_mode = 2;                // apply: 2 data-polling sweeps (precond_poll.cu), 1 flag sweeps, 0 launch per level
+  int build_mode = 0;                // factor: 1 flag sweep, 0 launch per level
+  dvec<int> sweep_meta_lower, sweep_meta_upper;  // int4 {row, first, last+1, 0} per level-ordered position (mode 2)
+  int poll_groups_lower = 0, poll_groups_upper = 0;  // scalar systems: groups of 4 level-padded rows
+  dvec<double> sweep_tmp, sweep_tmp2;  // forward-sweep result / copy of an in-place rhs (mode 2)
   // reference-style row partitions (block-Jacobi ILU across partitions); nparts <= 1: exact serial factor
   int nparts = 1;
   std::vector<int> h_parts;

@@ -35,6 +35,8 @@ void linsys_apply_ilu(su2b200_ctx* c, LinSys& ls, const double* x, double* y);
 void linsys_apply_lusgs(su2b200_ctx* c, LinSys& ls, const double* x, double* y);
 void linsys_build_prec(su2b200_ctx* c, LinSys& ls, int prec);
 void linsys_apply_prec(su2b200_ctx* c, LinSys& ls, int prec, const double* x, double* y);
+void linsys_check_sweeps(su2b200_ctx* c, LinSys& ls);  // throws if the sweep watchdog fired
+void ilu_apply_poll(su2b200_ctx* c, LinSys& ls, const double* x, double* y);  // precond_poll.cu
 double vec_dot(su2b200_ctx* c, LinSys& ls, const double* a, const double* b);
 void vec_axpy(su2b200_ctx* c, size_t n, double alpha, const double* x, double* y);           // y += alpha x
 void vec_axpby(su2b200_ctx* c, size_t n, double alpha, const double* x, double beta, double* y);  // y = alpha x + beta y

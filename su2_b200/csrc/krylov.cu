@@ -232,6 +232,7 @@ unsigned long linsys_solve(su2b200_ctx* c, LinSys& ls, int solver, int prec, dou
     default:
       throw Error("unknown linear solver");
   }
+  linsys_check_sweeps(c, ls);
   if (residual) *residual = res;
   return it;
 }

@@ -14,6 +14,7 @@
 #include "internal.hpp"
 #include "kernels.hpp"
 #include <algorithm>
+#include <cstdlib>
 
 namespace su2b200 {
 
@@ -310,10 +311,287 @@ __global__ void k_lusgs_backward_level(int n, const int* __restrict__ rows, int 
 }
 
 // ------------------------------------------------------------------------------------------------
+// Single-launch dependency-driven sweeps (the default schedule of the exact ILU0).
+// One launch performs a whole triangular sweep (or the whole factorisation): warps draw tickets from a global
+// counter and process the rows of the level-ordered list in ticket order; a row spins (acquire loads) on the
+// `ready` word of each row it depends on and publishes its own with a release store. Because the list is in level
+// order, every dependency of ticket t has a smaller ticket, i.e. was drawn by a warp that is already running, so the
+// scheme cannot deadlock whatever the residency of the grid (no cooperative launch, no cross-launch waiting).
+// A spin watchdog sets ctrl[1] and releases every waiter if a flag never arrives; the host turns that into an error.
+// Arithmetic and summation order per row are those of the level kernels above (== the reference's serial sweeps).
+// ------------------------------------------------------------------------------------------------
+__device__ __forceinline__ int ld_acquire(const int* p) {
+  int v;
+  asm volatile("ld.acquire.gpu.global.s32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+  return v;
+}
+__device__ __forceinline__ void st_release(int* p, int v) {
+  asm volatile("st.release.gpu.global.s32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
+}
+__device__ __forceinline__ bool wait_ready(const int* ready, int j, int epoch, int* ctrl) {
+  unsigned spins = 0;
+  while (ld_acquire(ready + j) != epoch) {
+    if ((++spins & 1023u) == 0) {
+      if (spins > (1u << 24)) atomicExch(ctrl + 1, 1);
+      if (ld_acquire(ctrl + 1) != 0) return false;
+    }
+  }
+  return true;
+}
+__device__ __forceinline__ int draw_ticket(int* ctrl, int lane) {
+  int t = 0;
+  if (lane == 0) t = atomicAdd(ctrl, 1);
+  return __shfl_sync(FULL, t, 0);
+}
+
+// ---- block systems (nVar 4/5): one warp per row -----------------------------------------------------
+template <int NV>
+__global__ void __launch_bounds__(128) k_sweep_forward(int n, const int* __restrict__ rows, int epoch, int* ready, int* ctrl,
+                                                       const int* __restrict__ row_ptr, const int* __restrict__ col_ind,
+                                                       const int* __restrict__ dia_ptr, const double* __restrict__ ILU,
+                                                       double* y) {
+  constexpr int LPB = NV * NV;
+  constexpr int CH = 4;
+  const int lane = threadIdx.x & 31;
+  const int q = lane < LPB ? lane : LPB - 1;
+  const int cc = q % NV;
+  for (;;) {
+    const int t = draw_ticket(ctrl, lane);
+    if (t >= n) return;
+    const int i = rows[t];
+    const int rb = row_ptr[i], di = dia_ptr[i];
+    double acc = 0.0;
+    for (int base = rb; base < di; base += CH) {
+      double a[CH];
+      int jj[CH];
+#pragma unroll
+      for (int k = 0; k < CH; ++k) {  // matrix entries do not depend on the sweep: fetch them before waiting
+        const int idx = base + k < di ? base + k : di - 1;
+        jj[k] = col_ind[idx];
+        a[k] = ILU[(size_t)idx * LPB + q];
+      }
+#pragma unroll
+      for (int k = 0; k < CH; ++k) {
+        if (base + k < di) {
+          if (!wait_ready(ready, jj[k], epoch, ctrl)) return;
+          acc += a[k] * __ldcg(y + (size_t)jj[k] * NV + cc);
+        }
+      }
+    }
+    double s = acc;
+#pragma unroll
+    for (int o = 1; o < NV; ++o) s += __shfl_down_sync(FULL, acc, o);
+    if (lane < LPB && cc == 0 && di > rb) {
+      y[(size_t)i * NV + q / NV] -= s;
+      __threadfence();
+    }
+    __syncwarp();
+    if (lane == 0) st_release(ready + i, epoch);
+  }
+}
+
+template <int NV>
+__global__ void __launch_bounds__(128) k_sweep_backward(int n, const int* __restrict__ rows, int end, int epoch, int* ready,
+                                                        int* ctrl, const int* __restrict__ row_ptr,
+                                                        const int* __restrict__ col_ind, const int* __restrict__ dia_ptr,
+                                                        const double* __restrict__ ILU, const double* __restrict__ invM,
+                                                        double* y) {
+  constexpr int LPB = NV * NV;
+  constexpr int CH = 4;
+  const int lane = threadIdx.x & 31;
+  const int q = lane < LPB ? lane : LPB - 1;
+  const int r = q / NV, cc = q % NV;
+  for (;;) {
+    const int t = draw_ticket(ctrl, lane);
+    if (t >= n) return;
+    const int i = rows[t];
+    const int ub = dia_ptr[i] + 1, re = row_ptr[i + 1];
+    const double minv = invM[(size_t)i * LPB + q];
+    const double yi = y[(size_t)i * NV + r];
+    double acc = 0.0;
+    for (int base = ub; base < re; base += CH) {
+      double a[CH];
+      int jj[CH];
+#pragma unroll
+      for (int k = 0; k < CH; ++k) {
+        const int idx = base + k < re ? base + k : re - 1;
+        jj[k] = col_ind[idx];
+        a[k] = ILU[(size_t)idx * LPB + q];
+      }
+#pragma unroll
+      for (int k = 0; k < CH; ++k) {
+        if (base + k < re && jj[k] < end) {
+          if (!wait_ready(ready, jj[k], epoch, ctrl)) return;
+          acc += a[k] * __ldcg(y + (size_t)jj[k] * NV + cc);
+        }
+      }
+    }
+    double s = acc;
+#pragma unroll
+    for (int o = 1; o < NV; ++o) s += __shfl_down_sync(FULL, acc, o);
+    const double aux_r = yi - s;  // valid on lanes r*NV
+    const double aux_c = __shfl_sync(FULL, aux_r, cc * NV);
+    const double prod = minv * aux_c;
+    double tsum = prod;
+#pragma unroll
+    for (int o = 1; o < NV; ++o) tsum += __shfl_down_sync(FULL, prod, o);
+    if (lane < LPB && cc == 0) {
+      y[(size_t)i * NV + r] = tsum;
+      __threadfence();
+    }
+    __syncwarp();
+    if (lane == 0) st_release(ready + i, epoch);
+  }
+}
+
+template <int NV>
+__global__ void __launch_bounds__(128) k_sweep_factor(int n, const int* __restrict__ rows, int end, int epoch, int* ready,
+                                                      int* ctrl, const int* __restrict__ row_ptr,
+                                                      const int* __restrict__ col_ind, const int* __restrict__ dia_ptr,
+                                                      double* ILU, double* invM) {
+  constexpr int LPB = NV * NV;
+  const int lane = threadIdx.x & 31;
+  const int q = lane < LPB ? lane : LPB - 1;
+  const bool act = lane < LPB;
+  const int r = q / NV, cc = q % NV;
+  for (;;) {
+    const int t = draw_ticket(ctrl, lane);
+    if (t >= n) return;
+    const int i = rows[t];
+    const int rb = row_ptr[i], re = row_ptr[i + 1], di = dia_ptr[i];
+    for (int idx = rb; idx < di; ++idx) {
+      const int j = col_ind[idx];
+      const double aij = __ldcg(ILU + (size_t)idx * LPB + q);  // own element (this lane wrote it, if at all)
+      if (!wait_ready(ready, j, epoch, ctrl)) return;
+      const double inv = __ldcg(invM + (size_t)j * LPB + q);
+      const double w = warp_matmul<NV>(aij, inv, r, cc);
+      for (int idx2 = dia_ptr[j] + 1; idx2 < row_ptr[j + 1]; ++idx2) {
+        const int k = col_ind[idx2];
+        if (k >= end) break;
+        int pos = -1;
+        for (int s = rb; s < re; ++s)
+          if (col_ind[s] == k) { pos = s; break; }
+        if (pos < 0) continue;
+        const double ajk = __ldcg(ILU + (size_t)idx2 * LPB + q);
+        const double aux = warp_matmul<NV>(w, ajk, r, cc);
+        if (act) ILU[(size_t)pos * LPB + q] -= aux;
+      }
+      if (act) ILU[(size_t)idx * LPB + q] = w;
+    }
+    // inverse of the updated diagonal block: gather it through the lanes that own its scalars
+    const double myd = __ldcg(ILU + (size_t)di * LPB + q);
+    double B[NV * NV], M[NV * NV];
+#pragma unroll
+    for (int k = 0; k < NV * NV; ++k) B[k] = __shfl_sync(FULL, myd, k);
+    matrix_inverse_d<NV>(B, M);
+    if (act) {
+      invM[(size_t)i * LPB + q] = M[q];
+      __threadfence();
+    }
+    __syncwarp();
+    if (lane == 0) st_release(ready + i, epoch);
+  }
+}
+
+// ---- scalar systems (nVar 1): one thread per row; `rows` is padded per level to a multiple of 32 with -1, so the
+//      rows of a warp never depend on each other ---------------------------------------------------------------------
+__global__ void __launch_bounds__(128) k_sweep_forward_s(int nWarpTickets, const int* __restrict__ rows, int epoch,
+                                                         int* ready, int* ctrl, const int* __restrict__ row_ptr,
+                                                         const int* __restrict__ col_ind, const int* __restrict__ dia_ptr,
+                                                         const double* __restrict__ ILU, double* y) {
+  const int lane = threadIdx.x & 31;
+  for (;;) {
+    const int t = draw_ticket(ctrl, lane);
+    if (t >= nWarpTickets) return;
+    const int i = rows[(size_t)t * 32 + lane];
+    if (i < 0) continue;
+    double acc = 0.0;
+    bool ok = true;  // on a watchdog abort keep drawing tickets (the warp-wide shuffle needs every lane) but do no work
+    const int rb = row_ptr[i], di = dia_ptr[i];
+    for (int idx = rb; idx < di && ok; ++idx) {
+      const int j = col_ind[idx];
+      const double a = ILU[idx];
+      ok = wait_ready(ready, j, epoch, ctrl);
+      if (ok) acc += a * __ldcg(y + j);
+    }
+    if (di > rb && ok) {
+      y[i] -= acc;
+      __threadfence();
+    }
+    st_release(ready + i, epoch);
+  }
+}
+__global__ void __launch_bounds__(128) k_sweep_backward_s(int nWarpTickets, const int* __restrict__ rows, int end, int epoch,
+                                                          int* ready, int* ctrl, const int* __restrict__ row_ptr,
+                                                          const int* __restrict__ col_ind, const int* __restrict__ dia_ptr,
+                                                          const double* __restrict__ ILU, const double* __restrict__ invM,
+                                                          double* y) {
+  const int lane = threadIdx.x & 31;
+  for (;;) {
+    const int t = draw_ticket(ctrl, lane);
+    if (t >= nWarpTickets) return;
+    const int i = rows[(size_t)t * 32 + lane];
+    if (i < 0) continue;
+    double acc = 0.0;
+    const double minv = invM[i], yi = y[i];
+    bool ok = true;
+    for (int idx = dia_ptr[i] + 1; idx < row_ptr[i + 1] && ok; ++idx) {
+      const int j = col_ind[idx];
+      if (j >= end) break;
+      const double a = ILU[idx];
+      ok = wait_ready(ready, j, epoch, ctrl);
+      if (ok) acc += a * __ldcg(y + j);
+    }
+    if (ok) y[i] = minv * (yi - acc);
+    __threadfence();
+    st_release(ready + i, epoch);
+  }
+}
+__global__ void __launch_bounds__(128) k_sweep_factor_s(int nWarpTickets, const int* __restrict__ rows, int end, int epoch,
+                                                        int* ready, int* ctrl, const int* __restrict__ row_ptr,
+                                                        const int* __restrict__ col_ind, const int* __restrict__ dia_ptr,
+                                                        double* ILU, double* invM) {
+  const int lane = threadIdx.x & 31;
+  for (;;) {
+    const int t = draw_ticket(ctrl, lane);
+    if (t >= nWarpTickets) return;
+    const int i = rows[(size_t)t * 32 + lane];
+    if (i < 0) continue;
+    const int rb = row_ptr[i], re = row_ptr[i + 1], di = dia_ptr[i];
+    bool ok = true;
+    for (int idx = rb; idx < di && ok; ++idx) {
+      const int j = col_ind[idx];
+      ok = wait_ready(ready, j, epoch, ctrl);
+      if (!ok) break;
+      const double w = ILU[idx] * __ldcg(invM + j);
+      for (int idx2 = dia_ptr[j] + 1; idx2 < row_ptr[j + 1]; ++idx2) {
+        const int k = col_ind[idx2];
+        if (k >= end) break;
+        int pos = -1;
+        for (int s = rb; s < re; ++s)
+          if (col_ind[s] == k) { pos = s; break; }
+        if (pos < 0) continue;
+        ILU[pos] -= w * __ldcg(ILU + idx2);
+      }
+      ILU[idx] = w;
+    }
+    double d = ILU[di], one = 1.0;
+    reg_pivot(d);
+    invM[i] = one / d;
+    __threadfence();
+    st_release(ready + i, epoch);
+  }
+}
+
+// ------------------------------------------------------------------------------------------------
 // Host: dependency levels of the owned sub-matrix (lower: deps j<i ; upper: deps j>i, j<Pd)
 // ------------------------------------------------------------------------------------------------
 static void build_levels(LinSys& ls) {
   if (ls.levels_ready) return;
+  // A/B switches: SU2B200_ILU_APPLY = 0 (launch per level) | 1 (flag sweeps) | 2 (data-polling sweeps, default)
+  //               SU2B200_ILU_BUILD = 0 (launch per level, default) | 1 (flag sweep)
+  if (const char* e = getenv("SU2B200_ILU_APPLY")) ls.sweep_mode = atoi(e);
+  if (const char* e = getenv("SU2B200_ILU_BUILD")) ls.build_mode = atoi(e);
   const int n = ls.Pd;
   const auto& rp = ls.h_row_ptr;
   const auto& ci = ls.h_col_ind;
@@ -348,7 +626,50 @@ static void build_levels(LinSys& ls) {
   }
   ls.nlev_upper = nl;
   bucket(nl, ls.lvl_ptr_upper, ls.lvl_rows_upper);
+  // ticket lists of the single-launch sweeps: block systems use the level-ordered list as is (a warp per row);
+  // scalar systems pad every level to a multiple of 32 so that the rows of one warp are mutually independent
+  auto padded = [&](const std::vector<int>& ptr, const dvec<int>& rows_d, dvec<int>& out, int& count) {
+    if (ls.nVar != 1) { count = n; return; }
+    const std::vector<int> rows = rows_d.to_host();
+    std::vector<int> pad;
+    pad.reserve(rows.size() + 32 * (ptr.size() - 1));
+    for (size_t l = 0; l + 1 < ptr.size(); ++l) {
+      for (int k = ptr[l]; k < ptr[l + 1]; ++k) pad.push_back(rows[k]);
+      while (pad.size() % 32) pad.push_back(-1);
+    }
+    count = (int)(pad.size() / 32);
+    out.upload(pad);
+  };
+  padded(ls.lvl_ptr_lower, ls.lvl_rows_lower, ls.sweep_rows_lower, ls.sweep_n_lower);
+  padded(ls.lvl_ptr_upper, ls.lvl_rows_upper, ls.sweep_rows_upper, ls.sweep_n_upper);
+  ls.sweep_ready.alloc(n > 0 ? n : 1);
+  ls.sweep_ready.zero();
+  ls.sweep_ctrl.alloc(2);
+  ls.sweep_ctrl.zero();
+  ls.sweep_epoch = 0;
+  if (!ls.h_sweep_ctrl) SU2B_CUDA(cudaMallocHost(&ls.h_sweep_ctrl, 2 * sizeof(int)));
+  SU2B_CUDA(cudaDeviceSynchronize());
   ls.levels_ready = true;
+}
+
+// grid of the persistent sweep kernels: enough warps to fill the machine, never more than there are tickets
+static inline int sweep_grid(int tickets) {
+  const int warpsPerBlock = 4;
+  return std::max(1, std::min((tickets + warpsPerBlock - 1) / warpsPerBlock, 148 * 16));
+}
+// new epoch + ticket reset (stream ordered); abort word is sticky until checked
+static inline int sweep_begin(su2b200_ctx* c, LinSys& ls) {
+  SU2B_CUDA(cudaMemsetAsync(ls.sweep_ctrl.p, 0, sizeof(int), c->stream));
+  return ++ls.sweep_epoch;
+}
+void linsys_check_sweeps(su2b200_ctx* c, LinSys& ls) {
+  if (!ls.sweep_ctrl.p || !ls.h_sweep_ctrl) return;
+  SU2B_CUDA(cudaMemcpyAsync(ls.h_sweep_ctrl, ls.sweep_ctrl.p, 2 * sizeof(int), cudaMemcpyDeviceToHost, c->stream));
+  SU2B_CUDA(cudaStreamSynchronize(c->stream));
+  if (ls.h_sweep_ctrl[1] != 0) {
+    SU2B_CUDA(cudaMemsetAsync(ls.sweep_ctrl.p, 0, 2 * sizeof(int), c->stream));
+    throw Error("triangular sweep watchdog fired: a row dependency never completed (corrupt level schedule?)");
+  }
 }
 
 // nnz-balanced partitions, CSysMatrix::Initialize (CSysMatrix.cpp:199-227)
@@ -373,7 +694,17 @@ static void ilu_build_impl(su2b200_ctx* c, LinSys& ls) {
   ls.ilu.alloc(nb);
   ls.invM.alloc((size_t)ls.Pd * NV * NV);
   SU2B_CUDA(cudaMemcpyAsync(ls.ilu.p, ls.A.p, nb * sizeof(double), cudaMemcpyDeviceToDevice, c->stream));
-  if (ls.nparts <= 1) {
+  if (ls.nparts <= 1) build_levels(ls);
+  if (ls.nparts <= 1 && ls.build_mode == 1) {
+    const int epoch = sweep_begin(c, ls);
+    if (NV == 1) {
+      SU2B_LAUNCH(c, k_sweep_factor_s, sweep_grid(ls.sweep_n_lower), 128, ls.sweep_n_lower, ls.sweep_rows_lower.p, ls.Pd,
+                  epoch, ls.sweep_ready.p, ls.sweep_ctrl.p, ls.row_ptr, ls.col_ind, ls.dia_ptr, ls.ilu.p, ls.invM.p);
+    } else {
+      SU2B_LAUNCH(c, k_sweep_factor<(NV == 1 ? 4 : NV)>, sweep_grid(ls.Pd), 128, ls.Pd, ls.lvl_rows_lower.p, ls.Pd, epoch,
+                  ls.sweep_ready.p, ls.sweep_ctrl.p, ls.row_ptr, ls.col_ind, ls.dia_ptr, ls.ilu.p, ls.invM.p);
+    }
+  } else if (ls.nparts <= 1) {
     build_levels(ls);
     for (int l = 0; l < ls.nlev_lower; ++l) {
       const int n = ls.lvl_ptr_lower[l + 1] - ls.lvl_ptr_lower[l];
@@ -390,8 +721,29 @@ static void ilu_build_impl(su2b200_ctx* c, LinSys& ls) {
 template <int NV>
 static void ilu_apply_impl(su2b200_ctx* c, LinSys& ls, const double* x, double* y) {
   const size_t n = (size_t)ls.Pd * NV;
+  if (ls.nparts <= 1) build_levels(ls);
+  if (ls.nparts <= 1 && ls.sweep_mode == 2) {
+    ilu_apply_poll(c, ls, x, y);
+    return;
+  }
   if (x != y) SU2B_CUDA(cudaMemcpyAsync(y, x, n * sizeof(double), cudaMemcpyDeviceToDevice, c->stream));
-  if (ls.nparts <= 1) {
+  if (ls.nparts <= 1 && ls.sweep_mode == 1) {
+    int epoch = sweep_begin(c, ls);
+    if (NV == 1) {
+      SU2B_LAUNCH(c, k_sweep_forward_s, sweep_grid(ls.sweep_n_lower), 128, ls.sweep_n_lower, ls.sweep_rows_lower.p, epoch,
+                  ls.sweep_ready.p, ls.sweep_ctrl.p, ls.row_ptr, ls.col_ind, ls.dia_ptr, ls.ilu.p, y);
+      epoch = sweep_begin(c, ls);
+      SU2B_LAUNCH(c, k_sweep_backward_s, sweep_grid(ls.sweep_n_upper), 128, ls.sweep_n_upper, ls.sweep_rows_upper.p, ls.Pd,
+                  epoch, ls.sweep_ready.p, ls.sweep_ctrl.p, ls.row_ptr, ls.col_ind, ls.dia_ptr, ls.ilu.p, ls.invM.p, y);
+    } else {
+      constexpr int NB = NV == 1 ? 4 : NV;
+      SU2B_LAUNCH(c, k_sweep_forward<NB>, sweep_grid(ls.Pd), 128, ls.Pd, ls.lvl_rows_lower.p, epoch, ls.sweep_ready.p,
+                  ls.sweep_ctrl.p, ls.row_ptr, ls.col_ind, ls.dia_ptr, ls.ilu.p, y);
+      epoch = sweep_begin(c, ls);
+      SU2B_LAUNCH(c, k_sweep_backward<NB>, sweep_grid(ls.Pd), 128, ls.Pd, ls.lvl_rows_upper.p, ls.Pd, epoch,
+                  ls.sweep_ready.p, ls.sweep_ctrl.p, ls.row_ptr, ls.col_ind, ls.dia_ptr, ls.ilu.p, ls.invM.p, y);
+    }
+  } else if (ls.nparts <= 1) {
     for (int l = 1; l < ls.nlev_lower; ++l) {
       const int m = ls.lvl_ptr_lower[l + 1] - ls.lvl_ptr_lower[l];
       SU2B_LAUNCH(c, k_ilu_forward_level<NV>, nblk((long)m * 32, 128), 128, m, ls.lvl_rows_lower.p + ls.lvl_ptr_lower[l], 0,

@@ -286,6 +286,12 @@ class FlowSolver:
         check(self.lib.su2b200_bench_spmv(self.ctx, int(which), int(reps), C.byref(ms)))
         return ms.value
 
+    def bench_prec(self, which=0, prec=capi.PREC_ILU, reps=5):
+        """(ms per build, ms per apply) of the preconditioner on the resident matrix."""
+        b, a = C.c_float(), C.c_float()
+        check(self.lib.su2b200_bench_prec(self.ctx, int(which), int(prec), int(reps), C.byref(b), C.byref(a)))
+        return b.value, a.value
+
 
 class LinearSystem:
     """CSysMatrix + CSysSolve stand-in with host-buffer entry points (HtD/DtH inside every call)."""
