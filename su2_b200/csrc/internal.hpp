@@ -141,7 +141,11 @@ struct LinSys {
   int sweep_epoch = 0;
   int* h_sweep_ctrl = nullptr;       // pinned
   int sweep_mode = 2;                // apply: 2 data-polling sweeps (precond_poll.cu), 1 flag sweeps, 0 launch per level
-  int build_mode = 0;                // factor: 1 flag sweep, 0 launch per level
+  int build_mode = 2;                // factor: 2 single-launch polling factorisation (precond_factor.cu), 1 flag sweep,
+                                     //         0 launch per level
+  bool factor_ready = false, factor_ok = false;
+  dvec<int> factor_desc, factor_ops;  // symbolic factorisation: row descriptors (level order) and update lists
+  int factor_own_cap = 0, factor_src_cap = 0;
   dvec<int> sweep_meta_lower, sweep_meta_upper;  // int4 {row, first, last+1, 0} per level-ordered position (mode 2)
   int poll_groups_lower = 0, poll_groups_upper = 0;  // scalar systems: groups of 4 level-padded rows
   dvec<double> sweep_tmp, sweep_tmp2;  // forward-sweep result / copy of an in-place rhs (mode 2)

@@ -37,6 +37,8 @@ void linsys_build_prec(su2b200_ctx* c, LinSys& ls, int prec);
 void linsys_apply_prec(su2b200_ctx* c, LinSys& ls, int prec, const double* x, double* y);
 void linsys_check_sweeps(su2b200_ctx* c, LinSys& ls);  // throws if the sweep watchdog fired
 void ilu_apply_poll(su2b200_ctx* c, LinSys& ls, const double* x, double* y);  // precond_poll.cu
+bool factor_symbolic(LinSys& ls);                                             // precond_factor.cu
+void ilu_factor_poll(su2b200_ctx* c, LinSys& ls);
 double vec_dot(su2b200_ctx* c, LinSys& ls, const double* a, const double* b);
 void vec_axpy(su2b200_ctx* c, size_t n, double alpha, const double* x, double* y);           // y += alpha x
 void vec_axpby(su2b200_ctx* c, size_t n, double alpha, const double* x, double beta, double* y);  // y = alpha x + beta y

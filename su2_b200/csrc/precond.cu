@@ -589,7 +589,7 @@ __global__ void __launch_bounds__(128) k_sweep_factor_s(int nWarpTickets, const 
 static void build_levels(LinSys& ls) {
   if (ls.levels_ready) return;
   // A/B switches: SU2B200_ILU_APPLY = 0 (launch per level) | 1 (flag sweeps) | 2 (data-polling sweeps, default)
-  //               SU2B200_ILU_BUILD = 0 (launch per level, default) | 1 (flag sweep)
+  //               SU2B200_ILU_BUILD = 0 (launch per level) | 1 (flag sweep) | 2 (polling factorisation, default)
   if (const char* e = getenv("SU2B200_ILU_APPLY")) ls.sweep_mode = atoi(e);
   if (const char* e = getenv("SU2B200_ILU_BUILD")) ls.build_mode = atoi(e);
   const int n = ls.Pd;
@@ -693,8 +693,12 @@ static void ilu_build_impl(su2b200_ctx* c, LinSys& ls) {
   const size_t nb = (size_t)ls.nnz * NV * NV;
   ls.ilu.alloc(nb);
   ls.invM.alloc((size_t)ls.Pd * NV * NV);
-  SU2B_CUDA(cudaMemcpyAsync(ls.ilu.p, ls.A.p, nb * sizeof(double), cudaMemcpyDeviceToDevice, c->stream));
   if (ls.nparts <= 1) build_levels(ls);
+  if (ls.nparts <= 1 && ls.build_mode == 2 && factor_symbolic(ls)) {
+    ilu_factor_poll(c, ls);  // reads A, writes ILU: no copy
+    return;
+  }
+  SU2B_CUDA(cudaMemcpyAsync(ls.ilu.p, ls.A.p, nb * sizeof(double), cudaMemcpyDeviceToDevice, c->stream));
   if (ls.nparts <= 1 && ls.build_mode == 1) {
     const int epoch = sweep_begin(c, ls);
     if (NV == 1) {

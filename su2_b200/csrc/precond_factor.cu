@@ -1,0 +1,340 @@
+// a17. ILU0 factorisation (CSysMatrix<T>::BuildILUPreconditioner, CSysMatrix.cpp:714-760) as ONE launch.
+//
+// Row i of the IKJ factorisation only ever writes row i, and needs, from every lower neighbour j, the inverse of the
+// factored diagonal (invM_j) and the upper blocks U_jk that meet row i's pattern. The host does the symbolic work once
+// per sparsity pattern: for every row the list of updates {source block (j,k), target slot (i,k), lower slot (i,j)}
+// in the reference's loop order, and which blocks the factorisation never modifies ("stable": on a hexahedral box all
+// off-diagonal upper blocks). The numeric kernel then
+//   * takes rows in dependency-level order, round-robin over the warps of a co-resident (cooperative) grid;
+//   * streams the row's own blocks and its stable sources from the input matrix A into shared memory with cp.async,
+//     one row ahead (descriptors two and three rows ahead), so that none of that is on the dependency chain;
+//   * waits for invM_j by polling the data itself (invM is pre-filled with a sentinel NaN payload);
+//   * does the 5x5 (4x4) products and the Gauss inversion cooperatively (one scalar per lane, shuffles);
+//   * writes the finished row to the ILU matrix and publishes invM_i (after a fence only if some block of the row
+//     is an unstable source for a later row).
+// A is read once and ILU written once: the A -> ILU copy of the level-scheduled path disappears.
+// The arithmetic per block, and its order, are those of ilu_factor_row (precond.cu) == the reference's.
+#include "internal.hpp"
+#include "kernels.hpp"
+#include <algorithm>
+
+namespace su2b200 {
+
+static constexpr unsigned FULLM = 0xffffffffu;
+static constexpr unsigned long long SENTINEL = 0xFFF8C0DEC0DE5A5AULL;
+static constexpr int MAXR = 16;  // blocks of a row held in shared memory (longer rows: level-scheduled fallback)
+static constexpr int MAXS = 12;  // stable sources staged ahead per row (the others are fetched when needed)
+static constexpr unsigned STABLE = 0x80000000u;
+#ifndef FACTOR_MIN_BLOCKS
+#define FACTOR_MIN_BLOCKS 6
+#endif
+
+__device__ __forceinline__ double ldr(const double* p) {
+  double v;
+  asm volatile("ld.relaxed.gpu.global.f64 %0, [%1];" : "=d"(v) : "l"(p) : "memory");
+  return v;
+}
+__device__ __forceinline__ void str(double* p, double v) {
+  asm volatile("st.relaxed.gpu.global.f64 [%0], %1;" ::"l"(p), "d"(v) : "memory");
+}
+__device__ __forceinline__ int ldr_i(const int* p) {
+  int v;
+  asm volatile("ld.relaxed.gpu.global.s32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+  return v;
+}
+__device__ __forceinline__ bool poll_f(const double* p, int* ctrl, double& out) {
+  unsigned spins = 0;
+  for (;;) {
+    const double v = ldr(p);
+    if ((unsigned long long)__double_as_longlong(v) != SENTINEL) { out = v; return true; }
+    if ((++spins & 1023u) == 0) {
+      if (spins > (1u << 24)) atomicExch(ctrl + 1, 1);
+      if (ldr_i(ctrl + 1) != 0) return false;
+    }
+  }
+}
+__device__ __forceinline__ void cp_async8(double* smem, const double* gmem) {
+  const unsigned s = (unsigned)__cvta_generic_to_shared(smem);
+  asm volatile("cp.async.ca.shared.global [%0], [%1], 8;" ::"r"(s), "l"(gmem) : "memory");
+}
+__device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
+template <int N>
+__device__ __forceinline__ void cp_async_wait() { asm volatile("cp.async.wait_group %0;" ::"n"(N) : "memory"); }
+
+__device__ __forceinline__ void fix_pivot(double& pivot) {
+  const double eps = (double)1e-12f;
+  if (fabs(pivot) < eps) pivot = copysign(eps, pivot);
+}
+
+template <int NV>
+__device__ __forceinline__ double wmatmul(double a, double b, int r, int cc) {
+  double s = 0.0;
+#pragma unroll
+  for (int m = 0; m < NV; ++m) s += __shfl_sync(FULLM, a, r * NV + m) * __shfl_sync(FULLM, b, m * NV + cc);
+  return s;
+}
+
+// Gauss elimination without pivoting + back substitution (CSysMatrix::MatrixInverse, CSysMatrix.cpp:1000-1058), one
+// scalar of A and of the inverse per lane; per element the same operations in the same order as the serial loops.
+template <int NV>
+__device__ __forceinline__ double winverse(double a, int r, int c, int q) {
+  double m = (r == c) ? 1.0 : 0.0;
+#pragma unroll
+  for (int j = 0; j < NV - 1; ++j) {
+    double pj = __shfl_sync(FULLM, a, j * NV + j);
+    fix_pivot(pj);
+    if (q == j * NV + j) a = pj;
+    const double arj = __shfl_sync(FULLM, a, r * NV + j);
+    const double w = arj / pj;
+    const double ajc = __shfl_sync(FULLM, a, j * NV + c);
+    const double mjc = __shfl_sync(FULLM, m, j * NV + c);
+    if (r > j) {
+      if (c >= j) a -= w * ajc;
+      if (c <= j) m -= w * mjc;
+    }
+  }
+#pragma unroll
+  for (int i = NV - 1; i >= 0; --i) {
+#pragma unroll
+    for (int j = i + 1; j < NV; ++j) {
+      const double aij = __shfl_sync(FULLM, a, i * NV + j);
+      const double mjc = __shfl_sync(FULLM, m, j * NV + c);
+      if (r == i) m -= aij * mjc;
+    }
+    double pii = __shfl_sync(FULLM, a, i * NV + i);
+    fix_pivot(pii);
+    if (r == i) m /= pii;
+  }
+  return m;
+}
+
+// row descriptor: a = {row, first entry, diagonal entry, one past the last entry}
+//                 b = {first op, op count, write-back mask (bit s: slot s changes), 1 if a fence must precede invM_i}
+struct RowDesc { int4 a, b; };
+
+template <int NV>
+__global__ void __launch_bounds__(128, FACTOR_MIN_BLOCKS) k_factor_poll(int n, int ownCap, int srcCap, const RowDesc* __restrict__ desc,
+                                                     const int2* __restrict__ ops,
+                                                     int* ctrl, const int* __restrict__ col_ind,
+                                                     const double* __restrict__ A, double* ILU, double* invM) {
+  constexpr int LPB = NV * NV;
+  extern __shared__ double smem[];  // [4 warps][2 buffers][ownCap blocks] then [4][2][srcCap]
+  double* sOwn = smem;
+  double* sSrc = smem + (size_t)4 * 2 * ownCap * LPB;
+  const int lane = threadIdx.x & 31, wib = threadIdx.x >> 5;
+  const int q = lane < LPB ? lane : LPB - 1;
+  const bool act = lane < LPB;
+  const int r = q / NV, cc = q % NV;
+  const int W = gridDim.x * (blockDim.x >> 5);
+  int t = blockIdx.x * (blockDim.x >> 5) + wib;
+  if (t >= n) return;
+
+  auto load_ops = [&](const RowDesc& d) -> int2 {  // lane u holds op u of the row (rows with more: fetched when used)
+    return lane < d.b.y ? ops[d.b.x + lane] : make_int2(0, 0);
+  };
+  auto load_cols = [&](const RowDesc& d) -> int {  // lane s holds the column of lower entry s
+    return d.a.y + lane < d.a.z ? col_ind[d.a.y + lane] : 0;
+  };
+  auto stage = [&](const RowDesc& d, int2 myop, int buf) {
+    const int nOwn = d.a.w - d.a.y;
+    double* own = sOwn + (size_t)(wib * 2 + buf) * ownCap * LPB;
+    double* src = sSrc + (size_t)(wib * 2 + buf) * srcCap * LPB;
+    if (act)
+      for (int s = 0; s < nOwn; ++s) cp_async8(own + s * LPB + q, A + (size_t)(d.a.y + s) * LPB + q);
+    const int ns = min(d.b.y, srcCap);
+    for (int u = 0; u < ns; ++u) {
+      const unsigned sidx = (unsigned)__shfl_sync(FULLM, myop.x, u);
+      if (act && (sidx & STABLE)) cp_async8(src + u * LPB + q, A + (size_t)(sidx & ~STABLE) * LPB + q);
+    }
+    cp_async_commit();
+  };
+
+  // pipeline: descriptor of row t+3W, ops/columns of row t+2W, staged data of row t+W, arithmetic of row t
+  RowDesc d0 = desc[t];
+  RowDesc d1 = t + W < n ? desc[t + W] : d0;
+  RowDesc d2 = t + 2 * W < n ? desc[t + 2 * W] : d1;
+  int2 op0 = load_ops(d0), op1 = load_ops(d1);
+  int col0 = load_cols(d0), col1 = load_cols(d1);
+  int buf = 0;
+  stage(d0, op0, buf);
+  for (; t < n; t += W) {
+    const RowDesc d3 = t + 3 * W < n ? desc[t + 3 * W] : d2;
+    int2 op2 = make_int2(0, 0);
+    int col2 = 0;
+    if (t + 2 * W < n) { op2 = load_ops(d2); col2 = load_cols(d2); }
+    if (t + W < n) stage(d1, op1, buf ^ 1); else cp_async_commit();
+    cp_async_wait<1>();
+    __syncwarp();
+
+    double* own = sOwn + (size_t)(wib * 2 + buf) * ownCap * LPB;
+    const double* src = sSrc + (size_t)(wib * 2 + buf) * srcCap * LPB;
+    const int i = d0.a.x, rb = d0.a.y, di = d0.a.z, re = d0.a.w;
+    const int nl = di - rb, nOps = d0.b.y;
+    int u = 0;
+    bool ok = true;
+    // first look at the inverse diagonals of the first lower neighbours, all in flight together
+    constexpr int LOOK = 4;
+    double look[LOOK];
+#pragma unroll
+    for (int s = 0; s < LOOK; ++s) {
+      const int j = __shfl_sync(FULLM, col0, s);
+      look[s] = s < nl ? ldr(invM + (size_t)j * LPB + q) : 0.0;
+    }
+    for (int s = 0; s < nl; ++s) {
+      const int j = s < 32 ? __shfl_sync(FULLM, col0, s) : col_ind[rb + s];
+      double inv = __longlong_as_double((long long)SENTINEL);
+#pragma unroll
+      for (int k = 0; k < LOOK; ++k)
+        if (s == k) inv = look[k];
+      if ((unsigned long long)__double_as_longlong(inv) == SENTINEL) ok = poll_f(invM + (size_t)j * LPB + q, ctrl, inv);
+      if (!__all_sync(FULLM, ok)) return;  // watchdog
+      const double aij = own[s * LPB + q];
+      const double w = wmatmul<NV>(aij, inv, r, cc);  // A_ij * inv(U_jj)
+      bool fenced = false;
+      for (;;) {
+        if (u >= nOps) break;
+        int2 op = u < 32 ? make_int2(__shfl_sync(FULLM, op0.x, u), __shfl_sync(FULLM, op0.y, u)) : ops[d0.b.x + u];
+        if ((op.y >> 16) != s) break;
+        const unsigned sidx = (unsigned)op.x;
+        double ajk;
+        if ((sidx & STABLE) && u < srcCap) ajk = src[u * LPB + q];
+        else if (sidx & STABLE) ajk = A[(size_t)(sidx & ~STABLE) * LPB + q];
+        else {  // block (j,k) was modified by row j: ordered after the invM_j we have just seen
+          if (!fenced) { __threadfence(); fenced = true; }
+          ajk = ldr(ILU + (size_t)sidx * LPB + q);
+        }
+        const double aux = wmatmul<NV>(w, ajk, r, cc);
+        if (act) own[(op.y & 0xffff) * LPB + q] -= aux;
+        ++u;
+      }
+      if (act) own[s * LPB + q] = w;
+      __syncwarp();
+    }
+    const double minv = winverse<NV>(own[nl * LPB + q], r, cc, q);
+    if (act) {
+      // every block goes to the ILU matrix (it is not a copy of A any more)
+      for (int s = 0; s < re - rb; ++s) ILU[(size_t)(rb + s) * LPB + q] = own[s * LPB + q];
+      if (d0.b.w) __threadfence();
+      str(invM + (size_t)i * LPB + q, minv);
+    }
+    __syncwarp();
+    d0 = d1; d1 = d2; d2 = d3;
+    op0 = op1; op1 = op2;
+    col0 = col1; col1 = col2;
+    buf ^= 1;
+  }
+}
+
+__global__ void k_fill_sentinel_f(size_t n, double* __restrict__ a) {
+  const double s = __longlong_as_double((long long)SENTINEL);
+  for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (size_t)gridDim.x * blockDim.x) a[i] = s;
+}
+
+// ---- host: symbolic factorisation -----------------------------------------------------------------------------------
+// returns false if a row does not fit the kernel's shared-memory slots (caller falls back to the level schedule)
+bool factor_symbolic(LinSys& ls) {
+  if (ls.factor_ready) return ls.factor_ok;
+  ls.factor_ready = true;
+  ls.factor_ok = false;
+  const int n = ls.Pd;
+  const auto& rp = ls.h_row_ptr;
+  const auto& ci = ls.h_col_ind;
+  const auto& dp = ls.h_dia_ptr;
+  for (int i = 0; i < n; ++i)
+    if (rp[i + 1] - rp[i] > MAXR || dp[i] - rp[i] > 32) return false;
+  // pass 1: update list per row, in the order of the reference's loops; mark the blocks that get modified
+  std::vector<long> opPtr(n + 1, 0);
+  std::vector<int2> opList;
+  opList.reserve((size_t)rp[n] / 2);
+  std::vector<unsigned char> modified(rp[n], 0);
+  for (int i = 0; i < n; ++i) {
+    const int rb = rp[i], re = rp[i + 1];
+    for (int idx = rb; idx < dp[i]; ++idx) {
+      const int j = ci[idx];
+      int s = rb;  // both rows are sorted by column: merge
+      for (int idx2 = dp[j] + 1; idx2 < rp[j + 1]; ++idx2) {
+        const int k = ci[idx2];
+        if (k >= n) break;
+        while (s < re && ci[s] < k) ++s;
+        if (s < re && ci[s] == k) {
+          opList.push_back(make_int2(idx2, ((idx - rb) << 16) | (s - rb)));
+          modified[s] = 1;
+        }
+      }
+    }
+    opPtr[i + 1] = (long)opList.size();
+  }
+  if (opList.size() >= (size_t)0x7fffffff) return false;
+  // pass 2: stable sources, write-back masks, fence flags; descriptors in level order
+  for (auto& op : opList)
+    if (!modified[op.x]) op.x = (int)((unsigned)op.x | STABLE);
+  const std::vector<int> rows = ls.lvl_rows_lower.to_host();
+  std::vector<RowDesc> desc(n);
+  int maxOwn = 1, maxOps = 0;
+  std::vector<int2> opsLevel;
+  opsLevel.reserve(opList.size());
+  for (int t = 0; t < n; ++t) {
+    const int i = rows[t];
+    RowDesc d;
+    d.a = make_int4(i, rp[i], dp[i], rp[i + 1]);
+    unsigned wb = 0;
+    int fence = 0;
+    for (int s = rp[i]; s < rp[i + 1]; ++s) {
+      const bool changes = s <= dp[i] || modified[s];
+      if (changes) wb |= 1u << (s - rp[i]);
+      if (s > dp[i] && modified[s]) fence = 1;  // an upper block that a later row reads from the ILU matrix
+    }
+    d.b = make_int4((int)opsLevel.size(), (int)(opPtr[i + 1] - opPtr[i]), (int)wb, fence);
+    for (long u = opPtr[i]; u < opPtr[i + 1]; ++u) opsLevel.push_back(opList[u]);
+    maxOwn = std::max(maxOwn, rp[i + 1] - rp[i]);
+    maxOps = std::max(maxOps, (int)(opPtr[i + 1] - opPtr[i]));
+    desc[t] = d;
+  }
+  static_assert(sizeof(RowDesc) == 32, "RowDesc layout");
+  ls.factor_desc.upload(reinterpret_cast<const int*>(desc.data()), desc.size() * 8);
+  if (opsLevel.empty()) opsLevel.push_back(make_int2(0, 0));
+  ls.factor_ops.upload(reinterpret_cast<const int*>(opsLevel.data()), opsLevel.size() * 2);
+  ls.factor_own_cap = maxOwn;
+  ls.factor_src_cap = std::max(1, std::min(maxOps, MAXS));
+  ls.factor_ok = true;
+  return true;
+}
+
+template <int NV>
+static void factor_launch(su2b200_ctx* c, LinSys& ls) {
+  int dev = 0, nsm = 0, perSm = 0;
+  int ownCap = ls.factor_own_cap, srcCap = ls.factor_src_cap;
+  const size_t smem = (size_t)4 * 2 * (ownCap + srcCap) * NV * NV * sizeof(double);
+  SU2B_CUDA(cudaGetDevice(&dev));
+  SU2B_CUDA(cudaDeviceGetAttribute(&nsm, cudaDevAttrMultiProcessorCount, dev));
+  SU2B_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&perSm, k_factor_poll<NV>, 128, smem));
+  static const int cap = getenv("SU2B200_FACTOR_BLOCKS") ? atoi(getenv("SU2B200_FACTOR_BLOCKS")) : 0;
+  if (cap > 0) perSm = std::min(perSm, cap);
+  SU2B_REQUIRE(perSm > 0, "ilu factor kernel does not fit an SM");
+  const int grid = std::max(1, std::min((ls.Pd + 3) / 4, nsm * perSm));
+  const size_t nInv = (size_t)ls.Pd * NV * NV;
+  SU2B_LAUNCH(c, k_fill_sentinel_f, (int)std::min<size_t>((nInv + 255) / 256, 148 * 8), 256, nInv, ls.invM.p);
+  int n = ls.Pd;
+  const RowDesc* desc = reinterpret_cast<const RowDesc*>(ls.factor_desc.p);
+  const int2* ops = reinterpret_cast<const int2*>(ls.factor_ops.p);
+  int* ctrl = ls.sweep_ctrl.p;
+  const int* ci = ls.col_ind;
+  const double* A = ls.A.p;
+  double* ilu = ls.ilu.p;
+  double* invM = ls.invM.p;
+  void* argv[] = {&n, &ownCap, &srcCap, &desc, &ops, &ctrl, &ci, &A, &ilu, &invM};
+  SU2B_CUDA(cudaLaunchCooperativeKernel((const void*)k_factor_poll<NV>, dim3(grid), dim3(128), argv, smem, c->stream));
+  c->launches++;
+}
+
+// ILU <- factor(A); requires build_levels(ls) and factor_symbolic(ls) == true
+void ilu_factor_poll(su2b200_ctx* c, LinSys& ls) {
+  switch (ls.nVar) {
+    case 1: factor_launch<1>(c, ls); break;  // one active lane per warp: latency-bound, the pipeline is what matters
+    case 4: factor_launch<4>(c, ls); break;
+    case 5: factor_launch<5>(c, ls); break;
+    default: throw Error("ilu_factor_poll: unsupported nVar");
+  }
+}
+
+}  // namespace su2b200
