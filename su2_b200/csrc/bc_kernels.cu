@@ -374,13 +374,22 @@ __global__ void k_friction_force(int nV, int Pd, int ngs, double factor, double 
   for (int k = 0; k < 3; ++k) { out[(size_t)t * 6 + k] = f[k]; out[(size_t)t * 6 + 3 + k] = m[k]; }
 }
 
-// sequential-in-thread sum over vertices (vertex order == reference order), 6 threads
+// sum over the vertices of a marker: 6 components x 32 contiguous chunks, each summed in vertex order, the chunks
+// then added in ascending order (fixed order; the reference adds vertex by vertex)
 __global__ void k_force_sum(int nV, const double* __restrict__ in, double* __restrict__ acc6) {
-  const int k = threadIdx.x;
-  if (k >= 6) return;
+  __shared__ double part[6][32];
+  const int k = threadIdx.x / 32, ch = threadIdx.x % 32;
+  const int per = (nV + 31) / 32;
+  const int t0 = min(ch * per, nV), t1 = min(t0 + per, nV);
   double s = 0.0;
-  for (int t = 0; t < nV; ++t) s += in[(size_t)t * 6 + k];
-  acc6[k] = s;
+  for (int t = t0; t < t1; ++t) s += in[(size_t)t * 6 + k];
+  part[k][ch] = s;
+  __syncthreads();
+  if (ch == 0) {
+    s = 0.0;
+    for (int q = 0; q < 32; ++q) s += part[k][q];
+    acc6[k] = s;
+  }
 }
 
 void flow_forces(su2b200_ctx* c, double* coeffs) {
@@ -420,7 +429,7 @@ void flow_forces(su2b200_ctx* c, double* coeffs) {
         SU2B_LAUNCH(c, k_friction_force<3>, nb, 128, m.nVertex, g.Pd, s.nG, factor, cfg.ref_length, cfg.ref_origin[0],
                     cfg.ref_origin[1], cfg.ref_origin[2], m.node.p, m.normal.p, g.coord.p, s.V.p, s.grad_prim.p, buf);
     }
-    SU2B_LAUNCH(c, k_force_sum, 1, 32, m.nVertex, buf, acc);
+    SU2B_LAUNCH(c, k_force_sum, 1, 192, m.nVertex, buf, acc);
     SU2B_CUDA(cudaMemcpyAsync(s.h_red, acc, 6 * sizeof(double), cudaMemcpyDeviceToHost, c->stream));
     SU2B_CUDA(cudaStreamSynchronize(c->stream));
     const double* F = s.h_red;
