@@ -9,7 +9,8 @@ import os
 import numpy as np
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "libsu2b200.so")
+# SU2B200_LIB selects another build of the same library (kernel tuning experiments)
+LIB_PATH = os.environ.get("SU2B200_LIB") or os.path.join(_HERE, "libsu2b200.so")
 
 c_ulong_p = C.POINTER(C.c_ulong)
 c_double_p = C.POINTER(C.c_double)

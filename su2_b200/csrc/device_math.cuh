@@ -46,9 +46,9 @@ __device__ __forceinline__ void inviscid_proj_flux(const double* V, const double
 }
 
 // inviscidProjJac, common.hpp:415-449. jac row-major [NV][NV].
-template <int ND>
+template <int ND, class JT>
 __device__ __forceinline__ void inviscid_proj_jac(double gamma, const double* vel, double energy,
-                                                  const double* normal, double scale, double* jac) {
+                                                  const double* normal, double scale, JT jac) {
   constexpr int NV = ND + 2;
   double projVel = dotN<ND>(vel, normal);
   double gm1 = gamma - 1;
@@ -172,9 +172,9 @@ __device__ __forceinline__ void p_matrix_inv(double gamma, double rho, const dou
 // (roe.hpp:87-214, :244-303), static grid, dissipation = 1 (NO_ROELOWDISS).
 // Vi/Vj: (reconstructed) primitives, entries [0, ND+4) used. normal = area vector i->j.
 // Outputs flux[NV]; if IMPLICIT also jac_i, jac_j (row-major NVxNV).
-template <int ND, bool IMPLICIT>
+template <int ND, bool IMPLICIT, class JT>
 __device__ __forceinline__ void roe_flux(const FlowParams& p, const double* Vi, const double* Vj,
-                                         const double* normal, double* flux, double* jac_i, double* jac_j) {
+                                         const double* normal, double* flux, JT jac_i, JT jac_j) {
   using I = PrimIdx<ND>;
   constexpr int NV = ND + 2;
   const double area = sqrt(dotN<ND>(normal, normal));
@@ -225,23 +225,38 @@ __device__ __forceinline__ void roe_flux(const FlowParams& p, const double* Vi, 
     inviscid_proj_jac<ND>(p.gamma, &Vj[I::VEL], Uj[ND + 1] / Uj[0], normal, p.roe_kappa, jac_j);
   }
 
-  double P[NV * NV], Pi[NV * NV];
-  p_matrix<ND>(p.gamma, rrho, rv, rq, rc, un, P);
-  p_matrix_inv<ND>(p.gamma, rrho, rv, rq, rc, un, Pi);
-
   double dU[NV];
 #pragma unroll
   for (int k = 0; k < NV; ++k) dU[k] = Uj[k] - Ui[k];
 
+  // D = P |Lambda| P^-1, accumulated one eigenvalue at a time: m_ij = sum_k P_ik lambda_k Pinv_kj in the reference's
+  // order of k. Column k of P and row k of P^-1 are regenerated for every k (the optimisation barrier keeps the
+  // compiler from merging the five evaluations back into two resident 5x5 matrices = 100 registers).
+  double m[NV * NV];
+#pragma unroll
+  for (int q = 0; q < NV * NV; ++q) m[q] = 0.0;
+#pragma unroll
+  for (int k = 0; k < NV; ++k) {
+    double rho_k = rrho, q_k = rq, c_k = rc;
+#ifdef __CUDA_ARCH__
+    asm volatile("" : "+d"(rho_k), "+d"(q_k), "+d"(c_k));
+#endif
+    double P[NV * NV], Pi[NV * NV];
+    p_matrix<ND>(p.gamma, rho_k, rv, q_k, c_k, un, P);
+    p_matrix_inv<ND>(p.gamma, rho_k, rv, q_k, c_k, un, Pi);
+#pragma unroll
+    for (int i = 0; i < NV; ++i) {
+      const double pl = P[i * NV + k] * lambda[k];
+#pragma unroll
+      for (int j = 0; j < NV; ++j) m[i * NV + j] += pl * Pi[k * NV + j];
+    }
+  }
   const double scale = (1 - p.roe_kappa) * area;  // * dissipation (== 1)
 #pragma unroll
   for (int i = 0; i < NV; ++i) {
 #pragma unroll
     for (int j = 0; j < NV; ++j) {
-      double m = 0.0;
-#pragma unroll
-      for (int k = 0; k < NV; ++k) m += P[i * NV + k] * lambda[k] * Pi[k * NV + j];
-      const double dDdU = m * scale;
+      const double dDdU = m[i * NV + j] * scale;
       flux[i] -= dDdU * dU[j];
       if (IMPLICIT) {
         jac_i[i * NV + j] += dDdU;
@@ -252,8 +267,8 @@ __device__ __forceinline__ void roe_flux(const FlowParams& p, const double* Vi, 
 }
 
 // scalarDissipationJacobian, common.hpp:533-549
-template <int ND>
-__device__ __forceinline__ void scalar_dissipation_jacobian(const double* V, double gamma, double dc, double* jac) {
+template <int ND, class JT>
+__device__ __forceinline__ void scalar_dissipation_jacobian(const double* V, double gamma, double dc, JT jac) {
   using I = PrimIdx<ND>;
   constexpr int NV = ND + 2;
 #pragma unroll
@@ -274,11 +289,11 @@ __device__ __forceinline__ void scalar_dissipation_jacobian(const double* V, dou
 // LEGACY = the boundary functor CAvgGrad_Flow (flow_diffusion.cpp:368-532): same flux, but its heat-flux Jacobian
 // uses cp/R * (k/cp + mu_t/Pr_t) (SetHeatFluxJacobian :489-532), which differs from the SIMD form when the mean cp
 // is not the gas cp (far-field state carries cp = k = 0, CEulerSolver.cpp:4990-4993).
-template <int ND, bool IMPLICIT, bool LEGACY = false>
+template <int ND, bool IMPLICIT, bool LEGACY = false, class JT = double*>
 __device__ __forceinline__ void viscous_terms(const FlowParams& p, const double* Vi, const double* Vj,
                                               const double* gi, const double* gj, const double* vec_ij,
                                               double area, const double* un, bool correct,
-                                              double* flux, double* jac_i, double* jac_j) {
+                                              double* flux, JT jac_i, JT jac_j) {
   using I = PrimIdx<ND>;
   constexpr int NV = ND + 2;
   constexpr int NG = ND + 1;
