@@ -443,6 +443,12 @@ void flow_forces(su2b200_ctx* c, double* coeffs) {
     }
     for (int k = 0; k < 3; ++k) { CF[k] += F[k]; CM[k] += F[3 + k]; }
   }
+  if (c->nranks > 1) {  // every coefficient is linear in the surface integrals: one sum over the ranks
+    double v[9] = {CL, CD, CSF, CF[0], CF[1], CF[2], CM[0], CM[1], CM[2]};
+    allreduce_vec(c, v, 9, 0);
+    CL = v[0]; CD = v[1]; CSF = v[2];
+    for (int k = 0; k < 3; ++k) { CF[k] = v[3 + k]; CM[k] = v[6 + k]; }
+  }
   if (coeffs) {
     coeffs[0] = CL; coeffs[1] = CD; coeffs[2] = CSF;
     coeffs[3] = CF[0]; coeffs[4] = CF[1]; coeffs[5] = CF[2];

@@ -91,6 +91,19 @@ void halo_exchange(su2b200_ctx* c, double* arr, int cnt) {
   SU2B_LAUNCH(c, k_unpack, nblk((long)nrecv * cnt, 256), 256, nrecv, cnt, c->p2p_recv_idx.p, c->p2p_recv_buf.p, arr);
 }
 
+// in-place allreduce of n (<= 32) host doubles; op: 0 sum, 2 max, 3 min (ncclRedOp_t)
+void allreduce_vec(su2b200_ctx* c, double* v, int n, int op) {
+  if (c->nranks <= 1) return;
+  SU2B_REQUIRE(c->nccl, "allreduce requested without a communicator");
+  SU2B_REQUIRE(n <= 32, "allreduce_vec: at most 32 values");
+  if (c->p2p_send_buf.n < 64) c->p2p_send_buf.alloc(64);
+  double* d = c->p2p_send_buf.p;
+  SU2B_CUDA(cudaMemcpyAsync(d, v, n * sizeof(double), cudaMemcpyHostToDevice, c->stream));
+  SU2B_NCCL(nccl().AllReduce(d, d, (size_t)n, 8, op, c->nccl, c->stream));
+  SU2B_CUDA(cudaMemcpyAsync(v, d, n * sizeof(double), cudaMemcpyDeviceToHost, c->stream));
+  SU2B_CUDA(cudaStreamSynchronize(c->stream));
+}
+
 double allreduce_sum(su2b200_ctx* c, double v) {
   if (c->nranks <= 1) return v;
   SU2B_REQUIRE(c->nccl, "allreduce requested without a communicator");

@@ -890,9 +890,25 @@ static void prepare_implicit_impl(su2b200_ctx* c, LinSys& ls, const double* dt, 
   if (e > b) LAUNCH(c, k_zero_range, nblk(e - b, 256), 256, res, sol, b, e);
   SU2B_CUDA(cudaMemcpyAsync(s.h_red, out, 3 * NV * sizeof(double), cudaMemcpyDeviceToHost, c->stream));
   SU2B_CUDA(cudaStreamSynchronize(c->stream));
+  double npts = (double)g.Pd;
+  if (c->nranks > 1) {  // CSolver::SetResidual_RMS: sums and point count over all ranks, maxima by MPI_MAX
+    double sums[NV + 1];
+    for (int v = 0; v < NV; ++v) sums[v] = s.h_red[v];
+    sums[NV] = npts;
+    allreduce_vec(c, sums, NV + 1, 0);
+    double mx[NV];
+    for (int v = 0; v < NV; ++v) mx[v] = s.h_red[NV + v];
+    allreduce_vec(c, mx, NV, 2);
+    for (int v = 0; v < NV; ++v) {
+      s.h_red[v] = sums[v];
+      if (mx[v] != s.h_red[NV + v]) s.h_red[2 * NV + v] = 0.0;  // the maximum is on another rank
+      s.h_red[NV + v] = mx[v];
+    }
+    npts = sums[NV];
+  }
   for (int v = 0; v < NV; ++v) {
-    // CSolver::SetResidual_RMS (CSolver.cpp:1951-1985), single rank: N = nPointDomain
-    double rms = sqrt(s.h_red[v] / (double)g.Pd);
+    // CSolver::SetResidual_RMS (CSolver.cpp:1951-1985): N = global nPointDomain
+    double rms = sqrt(s.h_red[v] / npts);
     const double eps = 1.0e-16;
     if (!(rms > eps * eps)) rms = (rms != rms) ? rms : eps * eps;
     if (out_rms) out_rms[v] = rms;
