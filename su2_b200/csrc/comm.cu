@@ -91,6 +91,13 @@ void halo_exchange(su2b200_ctx* c, double* arr, int cnt) {
   SU2B_LAUNCH(c, k_unpack, nblk((long)nrecv * cnt, 256), 256, nrecv, cnt, c->p2p_recv_idx.p, c->p2p_recv_buf.p, arr);
 }
 
+// in-stream, in-place sum of n device doubles over the ranks (no host synchronisation)
+void allreduce_dev_sum(su2b200_ctx* c, double* d, int n) {
+  if (c->nranks <= 1) return;
+  SU2B_REQUIRE(c->nccl, "allreduce requested without a communicator");
+  SU2B_NCCL(nccl().AllReduce(d, d, (size_t)n, 8, 0, c->nccl, c->stream));
+}
+
 // in-place allreduce of n (<= 32) host doubles; op: 0 sum, 2 max, 3 min (ncclRedOp_t)
 void allreduce_vec(su2b200_ctx* c, double* v, int n, int op) {
   if (c->nranks <= 1) return;

@@ -157,6 +157,7 @@ struct LinSys {
   std::vector<dvec<double>*> work;   // lazily grown pool of [P*nVar] vectors
   dvec<double> scalars;              // device scalars for reductions
   double* h_scalars = nullptr;       // pinned host mirror
+  double* h_mgs = nullptr;           // pinned: Hessenberg column of the device Gram-Schmidt
   ~LinSys();
   dvec<double>& vec(size_t i);
   size_t vecLen() const { return (size_t)P * nVar; }

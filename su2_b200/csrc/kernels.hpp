@@ -60,6 +60,7 @@ void turb_postprocessing(su2b200_ctx* c);
 // comm.cu
 void halo_exchange(su2b200_ctx* c, double* arr, int count_per_point);
 double allreduce_sum(su2b200_ctx* c, double v);
+void allreduce_dev_sum(su2b200_ctx* c, double* d, int n);       // device buffer, in stream
 void allreduce_vec(su2b200_ctx* c, double* v, int n, int op);  // op: 0 sum, 2 max, 3 min
 
 }  // namespace su2b200

@@ -67,6 +67,131 @@ static void generate_givens(double& dx, double& dy, double& s, double& c) {
   dy = 0.0;
 }
 
+
+// ---- ModGramSchmidt (CSysSolve.cpp:179-240) with the scalars kept on the device -----------------------------------
+// The reference alternates dot(w, v_k) and w -= h v_k, each dot a global reduction the host waits for. Here the axpy of
+// step k-1 is fused into the pass that computes the dot of step k, the coefficients stay in device memory (sc[]), the
+// 0.98 re-orthogonalisation test is evaluated on the device (the second projection's kernels exit at once when it is
+// not needed), and the host reads the finished Hessenberg column once per Krylov iteration. Values are bit-identical
+// to the unfused sequence (same elementwise fma, same two-stage reduction order).
+//   sc[0] coefficient of the pending axpy, sc[1] running norm^2, sc[2] threshold, sc[3] re-orthogonalise flag,
+//   sc[4] failure flag, sc[5] final norm, sc[6] reduction result, sc[8+k] = H(k, i)
+constexpr int MGS_BLOCKS = 148 * 4;
+__global__ void __launch_bounds__(256) k_mgs_dot(size_t n_owned, size_t n_all, double* __restrict__ w,
+                                                  const double* __restrict__ vprev, const double* __restrict__ vk,
+                                                  const double* __restrict__ sc, int need_flag,
+                                                  double* __restrict__ part) {
+  if (need_flag && sc[3] == 0.0) return;
+  const double coef = vprev ? sc[0] : 0.0;
+  double s = 0.0;
+  for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < n_all; i += (size_t)gridDim.x * blockDim.x) {
+    double wi = w[i];
+    if (vprev) { wi += -coef * vprev[i]; w[i] = wi; }
+    if (i < n_owned) s += wi * (vk ? vk[i] : wi);
+  }
+  __shared__ double sm[32];
+  for (int o = 16; o > 0; o >>= 1) s += __shfl_xor_sync(0xffffffffu, s, o);
+  const int wp = threadIdx.x >> 5, l = threadIdx.x & 31;
+  if (l == 0) sm[wp] = s;
+  __syncthreads();
+  if (wp == 0) {
+    s = (l < (blockDim.x >> 5)) ? sm[l] : 0.0;
+    for (int o = 16; o > 0; o >>= 1) s += __shfl_xor_sync(0xffffffffu, s, o);
+    if (l == 0) part[blockIdx.x] = s;
+  }
+}
+__global__ void k_mgs_stage2(int nb, const double* __restrict__ part, double* __restrict__ sc, int need_flag) {
+  if (need_flag && sc[3] == 0.0) { if (threadIdx.x == 0) sc[6] = 0.0; return; }
+  double s = 0.0;
+  for (int i = threadIdx.x; i < nb; i += blockDim.x) s += part[i];
+  __shared__ double sm[32];
+  for (int o = 16; o > 0; o >>= 1) s += __shfl_xor_sync(0xffffffffu, s, o);
+  const int wp = threadIdx.x >> 5, l = threadIdx.x & 31;
+  if (l == 0) sm[wp] = s;
+  __syncthreads();
+  if (wp == 0) {
+    s = (l < (blockDim.x >> 5)) ? sm[l] : 0.0;
+    for (int o = 16; o > 0; o >>= 1) s += __shfl_xor_sync(0xffffffffu, s, o);
+    if (l == 0) sc[6] = s;
+  }
+}
+// mode 0: nrm = w.w ; 1: first projection on v_k ; 2: second projection (if flagged) ; 3: final norm
+__global__ void k_mgs_logic(double* __restrict__ sc, int mode, int k) {
+  const double reorth = 0.98;
+  const double prod = sc[6];
+  if (mode == 0) {
+    sc[1] = prod; sc[2] = prod * reorth; sc[0] = 0.0; sc[3] = 0.0;
+    sc[4] = ((prod <= 0.0) || (prod != prod)) ? 1.0 : 0.0;
+  } else if (mode == 1) {
+    sc[8 + k] = prod;
+    sc[0] = prod;
+    if (prod * prod > sc[2]) {
+      sc[3] = 1.0;
+    } else {
+      sc[3] = 0.0;
+      double nrm = sc[1] - prod * prod;
+      nrm = fmax(nrm, 0.0);
+      sc[1] = nrm; sc[2] = nrm * reorth;
+    }
+  } else if (mode == 2) {
+    if (sc[3] == 0.0) return;
+    const double h = sc[8 + k] + prod;
+    sc[8 + k] = h;
+    sc[0] = prod;
+    sc[3] = 0.0;
+    double nrm = sc[1] - h * h;
+    nrm = fmax(nrm, 0.0);
+    sc[1] = nrm; sc[2] = nrm * reorth;
+  } else {
+    const double nrm = sqrt(prod);
+    sc[5] = nrm;
+    sc[8 + k] = nrm;
+  }
+}
+__global__ void k_div_dev(size_t n, const double* __restrict__ sc, double* __restrict__ x) {
+  const double d = sc[5];
+  for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (size_t)gridDim.x * blockDim.x)
+    x[i] /= d;
+}
+
+// orthogonalise w = V(i+1) against V(0..i); fills H(0..i+1, i) through `hcol`
+template <class VecFn>
+static void mod_gram_schmidt_device(su2b200_ctx* c, LinSys& ls, int i, VecFn V, double* hcol) {
+  const size_t n_all = ls.vecLen(), n_owned = (size_t)ls.Pd * ls.nVar;
+  if (ls.scalars.n < 4096) {
+    ls.scalars.alloc(4096);
+    ls.scalars.zero(c->stream);
+  }
+  if (!ls.h_mgs) SU2B_CUDA(cudaMallocHost(&ls.h_mgs, 1100 * sizeof(double)));
+  double* part = ls.scalars.p + 1024;  // [MGS_BLOCKS] (the first DOT_BLOCKS + 64 entries belong to vec_dot)
+  double* sc = ls.scalars.p + 2048;    // [8 + m + 2]
+  const int nb = (int)std::min<size_t>((n_all + 255) / 256, MGS_BLOCKS);
+  double* w = V(i + 1);
+  auto dot = [&](const double* vprev, const double* vk, int need_flag, int mode, int k) {
+    {
+      ProfScope prof_(c, PROF_DOT);
+      SU2B_LAUNCH(c, k_mgs_dot, nb, 256, n_owned, n_all, w, vprev, vk, (const double*)sc, need_flag, part);
+      SU2B_LAUNCH(c, k_mgs_stage2, 1, 256, nb, (const double*)part, sc, need_flag);
+      allreduce_dev_sum(c, sc + 6, 1);
+      SU2B_LAUNCH(c, k_mgs_logic, 1, 1, sc, mode, k);
+    }
+  };
+  dot(nullptr, nullptr, 0, 0, 0);  // nrm = w.w
+  for (int k = 0; k <= i; ++k) {
+    dot(k ? V(k - 1) : nullptr, V(k), 0, 1, k);  // pending axpy with v_{k-1}, then w.v_k
+    dot(V(k), V(k), 1, 2, k);                    // second projection on v_k, only if the device flag is set
+  }
+  dot(V(i), nullptr, 0, 3, i + 1);               // last axpy, then |w|
+  {
+    ProfScope prof_(c, PROF_VECOPS);
+    SU2B_LAUNCH(c, k_div_dev, (int)std::min<size_t>((n_all + 255) / 256, 148 * 8), 256, n_all, (const double*)sc, w);
+  }
+  SU2B_CUDA(cudaMemcpyAsync(ls.h_mgs, sc, (size_t)(8 + i + 2) * sizeof(double), cudaMemcpyDeviceToHost, c->stream));
+  SU2B_CUDA(cudaStreamSynchronize(c->stream));
+  if (ls.h_mgs[4] != 0.0) throw Error("FGMRES orthogonalization failed, linear solver diverged.");
+  for (int k = 0; k <= i + 1; ++k) hcol[k] = ls.h_mgs[8 + k];
+}
+
 static unsigned long fgmres(su2b200_ctx* c, LinSys& ls, int prec, double tol, int m, const double* b, double* x,
                             bool xIsZero, double* residual) {
   SU2B_REQUIRE(m >= 1, "Number of linear solver iterations must be greater than 0.");
@@ -101,28 +226,9 @@ static unsigned long fgmres(su2b200_ctx* c, LinSys& ls, int prec, double tol, in
     linsys_spmv(c, ls, Z(i), V(i + 1));
     // ModGramSchmidt(i, H, V)
     {
-      const double reorth = 0.98;
-      double* w = V(i + 1);
-      double nrm = vec_dot(c, ls, w, w);
-      double thr = nrm * reorth;
-      if ((nrm <= 0.0) || (nrm != nrm)) throw Error("FGMRES orthogonalization failed, linear solver diverged.");
-      for (int k = 0; k < i + 1; k++) {
-        double prod = vec_dot(c, ls, w, V(k));
-        double h_ki = prod;
-        vec_axpy(c, n, -prod, V(k), w);
-        if (prod * prod > thr) {
-          prod = vec_dot(c, ls, w, V(k));
-          h_ki += prod;
-          vec_axpy(c, n, -prod, V(k), w);
-        }
-        Hm(k, i) = h_ki;
-        nrm -= h_ki * h_ki;
-        nrm = std::max(nrm, 0.0);
-        thr = nrm * reorth;
-      }
-      nrm = sqrt(vec_dot(c, ls, w, w));
-      Hm(i + 1, i) = nrm;
-      SU2B_LAUNCH(c, k_div, vgrid(n), 256, n, nrm, w);
+      std::vector<double> hcol(i + 2, 0.0);
+      mod_gram_schmidt_device(c, ls, i, V, hcol.data());
+      for (int k = 0; k <= i + 1; ++k) Hm(k, i) = hcol[k];
     }
     for (int k = 0; k < i; k++) apply_givens(sn[k], cs[k], Hm(k, i), Hm(k + 1, i));
     generate_givens(Hm(i, i), Hm(i + 1, i), sn[i], cs[i]);

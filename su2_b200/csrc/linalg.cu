@@ -19,6 +19,7 @@ static constexpr unsigned FULL = 0xffffffffu;
 LinSys::~LinSys() {
   for (auto* v : work) delete v;
   if (h_scalars) cudaFreeHost(h_scalars);
+  if (h_mgs) cudaFreeHost(h_mgs);
 }
 dvec<double>& LinSys::vec(size_t i) {
   while (work.size() <= i) work.push_back(new dvec<double>());
@@ -104,7 +105,7 @@ __global__ void k_dot_stage2(int nb, const double* __restrict__ part, double* __
 }
 
 static void ensure_scalars(LinSys& ls) {
-  if (ls.scalars.n < (size_t)DOT_BLOCKS + 64) ls.scalars.alloc(DOT_BLOCKS + 64);
+  if (ls.scalars.n < 4096) ls.scalars.alloc(4096);  // [0,1024) vec_dot, [1024,4096) device Gram-Schmidt (krylov.cu)
   if (!ls.h_scalars) SU2B_CUDA(cudaMallocHost(&ls.h_scalars, 64 * sizeof(double)));
 }
 
