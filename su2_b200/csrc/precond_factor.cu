@@ -231,6 +231,130 @@ __global__ void __launch_bounds__(128, FACTOR_MIN_BLOCKS) k_factor_poll(int n, i
   }
 }
 
+// ---- scalar systems (SA): SROWS_F rows per warp, SGRP lanes per row all doing the same arithmetic (lane 0 stores) -------
+// The block kernel with nVar = 1 keeps one lane of 32 busy and is bound by its own instruction stream; here a row is a
+// handful of registers: own[8] and up to four stable sources are prefetched one row ahead, updates select their target
+// with predicates (no dynamic register index). Rows that do not fit (more than 8 entries, 4 lower neighbours or 4
+// updates, or an unstable source) take the in-memory path below, same arithmetic.
+static constexpr int SGRP = 4, SROWS_F = 32 / SGRP, SOWN = 8, SLOW = 4;
+struct ScalarRow {
+  double own[SOWN], src[SLOW];
+  int col[SLOW];
+  int2 op[SLOW];
+};
+__device__ __forceinline__ void fetch_scalar_row(ScalarRow& r, const RowDesc& d, const int2* __restrict__ ops,
+                                                 const int* __restrict__ col_ind, const double* __restrict__ A) {
+  const bool ok = d.a.x >= 0 && d.b.z != 0;
+#pragma unroll
+  for (int s = 0; s < SOWN; ++s) r.own[s] = (ok && d.a.y + s < d.a.w) ? A[d.a.y + s] : 0.0;
+#pragma unroll
+  for (int s = 0; s < SLOW; ++s) {
+    r.col[s] = (ok && d.a.y + s < d.a.z) ? col_ind[d.a.y + s] : 0;
+    r.op[s] = (ok && s < d.b.y) ? ops[d.b.x + s] : make_int2(0, -1);
+  }
+#pragma unroll
+  for (int s = 0; s < SLOW; ++s) r.src[s] = (ok && s < d.b.y) ? A[(unsigned)r.op[s].x & ~STABLE] : 0.0;
+}
+
+__global__ void __launch_bounds__(128) k_factor_poll_s(int nSlots, const RowDesc* __restrict__ desc,
+                                                       const int2* __restrict__ ops, int* ctrl,
+                                                       const int* __restrict__ col_ind, const double* __restrict__ A,
+                                                       double* ILU, double* invM) {
+  const int lane = threadIdx.x & 31, sub = lane / SGRP;
+  const bool writer = (lane % SGRP) == 0;
+  const int W = gridDim.x * (blockDim.x >> 5) * SROWS_F;
+  int t = (blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5)) * SROWS_F + sub;
+  if (t >= nSlots) return;
+  RowDesc d0 = desc[t];
+  RowDesc d1 = t + W < nSlots ? desc[t + W] : d0;
+  RowDesc d2 = t + 2 * W < nSlots ? desc[t + 2 * W] : d1;
+  ScalarRow cur, nxt;
+  fetch_scalar_row(cur, d0, ops, col_ind, A);
+  nxt = cur;
+  bool ok = true;
+  for (; t < nSlots; t += W) {
+    const RowDesc d3 = t + 3 * W < nSlots ? desc[t + 3 * W] : d2;
+    if (t + W < nSlots) fetch_scalar_row(nxt, d1, ops, col_ind, A);
+    const int i = d0.a.x, rb = d0.a.y, di = d0.a.z, re = d0.a.w;
+    const int nl = di - rb;
+    if (i >= 0 && ok) {
+      if (d0.b.z != 0) {
+        // ---- register path ----
+        double look[SLOW];
+#pragma unroll
+        for (int s = 0; s < SLOW; ++s) look[s] = s < nl ? ldr(invM + cur.col[s]) : 0.0;
+#pragma unroll
+        for (int s = 0; s < SLOW; ++s) {
+          if (s < nl && ok) {
+            double inv = look[s];
+            if ((unsigned long long)__double_as_longlong(inv) == SENTINEL) ok = poll_f(invM + cur.col[s], ctrl, inv);
+            if (ok) {
+              const double w = cur.own[s] * inv;
+#pragma unroll
+              for (int u = 0; u < SLOW; ++u) {
+                if (u < d0.b.y && (cur.op[u].y >> 16) == s) {
+                  const int pos = cur.op[u].y & 0xffff;
+                  const double aux = w * cur.src[u];
+#pragma unroll
+                  for (int p = 0; p < SOWN; ++p)
+                    if (p == pos) cur.own[p] -= aux;
+                }
+              }
+              cur.own[s] = w;
+            }
+          }
+        }
+        if (ok) {
+          double dgn = 0.0;
+#pragma unroll
+          for (int p = 0; p < SOWN; ++p)
+            if (p == nl) dgn = cur.own[p];
+          fix_pivot(dgn);
+          const double minv = 1.0 / dgn;
+          if (writer) {
+#pragma unroll
+            for (int p = 0; p < SOWN; ++p)
+              if (rb + p < re) ILU[rb + p] = cur.own[p];
+            if (d0.b.w) __threadfence();  // a modified upper entry of this row is read by a later row
+            str(invM + i, minv);
+          }
+        }
+      } else {
+        // ---- in-memory path: the row is copied to the ILU array and updated there (writer lane only) ----
+        if (writer) {
+          for (int s = rb; s < re; ++s) ILU[s] = A[s];
+          int u = d0.b.x;
+          const int uEnd = d0.b.x + d0.b.y;
+          for (int s = 0; s < nl && ok; ++s) {
+            double inv;
+            ok = poll_f(invM + col_ind[rb + s], ctrl, inv);
+            if (!ok) break;
+            __threadfence();
+            const double w = ILU[rb + s] * inv;
+            while (u < uEnd && (ops[u].y >> 16) == s) {
+              const int2 op = ops[u];
+              const unsigned sidx = (unsigned)op.x;
+              const double ajk = (sidx & STABLE) ? A[sidx & ~STABLE] : ldr(ILU + sidx);
+              ILU[rb + (op.y & 0xffff)] -= w * ajk;
+              ++u;
+            }
+            ILU[rb + s] = w;
+          }
+          if (ok) {
+            double dgn = ILU[di];
+            fix_pivot(dgn);
+            __threadfence();
+            str(invM + i, 1.0 / dgn);
+          }
+        }
+      }
+    }
+    ok = __all_sync(FULLM, ok);  // after the watchdog fired every lane idles through its remaining rows
+    d0 = d1; d1 = d2; d2 = d3;
+    cur = nxt;
+  }
+}
+
 __global__ void k_fill_sentinel_f(size_t n, double* __restrict__ a) {
   const double s = __longlong_as_double((long long)SENTINEL);
   for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (size_t)gridDim.x * blockDim.x) a[i] = s;
@@ -297,6 +421,27 @@ bool factor_symbolic(LinSys& ls) {
     desc[t] = d;
   }
   static_assert(sizeof(RowDesc) == 32, "RowDesc layout");
+  if (ls.nVar == 1) {
+    // scalar kernel: every level padded to SROWS_F slots (rows of a warp never depend on one another), b.z = 1 for
+    // rows that fit the register path
+    std::vector<RowDesc> padded;
+    padded.reserve(desc.size() + (size_t)SROWS_F * ls.lvl_ptr_lower.size());
+    RowDesc empty;
+    empty.a = make_int4(-1, 0, 0, 0);
+    empty.b = make_int4(0, 0, 0, 0);
+    for (size_t l = 0; l + 1 < ls.lvl_ptr_lower.size(); ++l) {
+      for (int t = ls.lvl_ptr_lower[l]; t < ls.lvl_ptr_lower[l + 1]; ++t) {
+        RowDesc d = desc[t];
+        bool fast = d.a.w - d.a.y <= SOWN && d.a.z - d.a.y <= SLOW && d.b.y <= SLOW;
+        for (int u = 0; u < d.b.y && fast; ++u) fast = ((unsigned)opsLevel[d.b.x + u].x & STABLE) != 0;
+        d.b.z = fast ? 1 : 0;
+        padded.push_back(d);
+      }
+      while (padded.size() % SROWS_F) padded.push_back(empty);
+    }
+    desc.swap(padded);
+    ls.factor_slots = (int)desc.size();
+  }
   ls.factor_desc.upload(reinterpret_cast<const int*>(desc.data()), desc.size() * 8);
   if (opsLevel.empty()) opsLevel.push_back(make_int2(0, 0));
   ls.factor_ops.upload(reinterpret_cast<const int*>(opsLevel.data()), opsLevel.size() * 2);
@@ -333,10 +478,35 @@ static void factor_launch(su2b200_ctx* c, LinSys& ls) {
   c->launches++;
 }
 
+static void factor_launch_scalar(su2b200_ctx* c, LinSys& ls) {
+  int dev = 0, nsm = 0, perSm = 0;
+  SU2B_CUDA(cudaGetDevice(&dev));
+  SU2B_CUDA(cudaDeviceGetAttribute(&nsm, cudaDevAttrMultiProcessorCount, dev));
+  SU2B_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&perSm, k_factor_poll_s, 128, 0));
+  static const int cap = getenv("SU2B200_FACTOR_BLOCKS_S") ? atoi(getenv("SU2B200_FACTOR_BLOCKS_S")) : 0;
+  if (cap > 0) perSm = std::min(perSm, cap);
+  SU2B_REQUIRE(perSm > 0, "scalar ilu factor kernel does not fit an SM");
+  int nSlots = ls.factor_slots;
+  const int warps = (nSlots + SROWS_F - 1) / SROWS_F;
+  const int grid = std::max(1, std::min((warps + 3) / 4, nsm * perSm));
+  SU2B_LAUNCH(c, k_fill_sentinel_f, (int)std::min<size_t>(((size_t)ls.Pd + 255) / 256, 148 * 8), 256, (size_t)ls.Pd,
+              ls.invM.p);
+  const RowDesc* desc = reinterpret_cast<const RowDesc*>(ls.factor_desc.p);
+  const int2* ops = reinterpret_cast<const int2*>(ls.factor_ops.p);
+  int* ctrl = ls.sweep_ctrl.p;
+  const int* ci = ls.col_ind;
+  const double* A = ls.A.p;
+  double* ilu = ls.ilu.p;
+  double* invM = ls.invM.p;
+  void* argv[] = {&nSlots, &desc, &ops, &ctrl, &ci, &A, &ilu, &invM};
+  SU2B_CUDA(cudaLaunchCooperativeKernel((const void*)k_factor_poll_s, dim3(grid), dim3(128), argv, 0, c->stream));
+  c->launches++;
+}
+
 // ILU <- factor(A); requires build_levels(ls) and factor_symbolic(ls) == true
 void ilu_factor_poll(su2b200_ctx* c, LinSys& ls) {
   switch (ls.nVar) {
-    case 1: factor_launch<1>(c, ls); break;  // one active lane per warp: latency-bound, the pipeline is what matters
+    case 1: factor_launch_scalar(c, ls); break;
     case 4: factor_launch<4>(c, ls); break;
     case 5: factor_launch<5>(c, ls); break;
     default: throw Error("ilu_factor_poll: unsupported nVar");
