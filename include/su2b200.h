@@ -293,6 +293,11 @@ int su2b200_linsys_create(su2b200_ctx* ctx, int which, int nVar, unsigned long n
 /* number of row partitions of the preconditioner sweeps: LINEAR_SOLVER_PREC_THREADS / omp_partitions
  * (CSysMatrix.cpp:199-227); 1 = the serial reference order (level-scheduled on the device) */
 int su2b200_linsys_set_partitions(su2b200_ctx* ctx, int which, int nparts);
+/* schedule of the exact (nparts == 1) ILU0 kernels, for A/B tests; -1 keeps the current value.
+ * apply_mode: 0 one launch per dependency level, 1 single-launch flag sweeps, 2 single-launch data-polling sweeps
+ * (default); build_mode: 0 one launch per level, 1 flag sweep, 2 single-launch polling factorisation (default).
+ * All schedules perform the arithmetic of CSysMatrix.cpp:673-823 in the same order. */
+int su2b200_linsys_set_schedule(su2b200_ctx* ctx, int which, int apply_mode, int build_mode);
 /* CSysMatrix::HtDTransfer (CSysMatrixGPU.cu:59-64) */
 int su2b200_linsys_set_matrix(su2b200_ctx* ctx, int which, const double* blocks);
 /* CSysMatrix::GPUMatrixVectorProduct (CSysMatrixGPU.cu:66-86) == MatrixVectorProduct (CSysMatrix.cpp:617-645):

@@ -358,6 +358,14 @@ int su2b200_linsys_set_partitions(su2b200_ctx* c, int which, int nparts) {
   API_END
 }
 
+int su2b200_linsys_set_schedule(su2b200_ctx* c, int which, int apply_mode, int build_mode) {
+  API_BEGIN
+  auto& ls = get_sys(c, which);
+  if (apply_mode >= 0) { SU2B_REQUIRE(apply_mode <= 2, "apply_mode: 0 levels, 1 flag sweeps, 2 polling sweeps"); ls.sweep_mode = apply_mode; }
+  if (build_mode >= 0) { SU2B_REQUIRE(build_mode <= 2, "build_mode: 0 levels, 1 flag sweep, 2 polling factorisation"); ls.build_mode = build_mode; }
+  API_END
+}
+
 int su2b200_linsys_set_matrix(su2b200_ctx* c, int which, const double* blocks) {
   API_BEGIN
   auto& ls = get_sys(c, which);

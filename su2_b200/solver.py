@@ -319,6 +319,10 @@ class LinearSystem:
     def set_partitions(self, n):
         check(self.lib.su2b200_linsys_set_partitions(self.ctx, self.which, int(n)))
 
+    def set_schedule(self, apply_mode=-1, build_mode=-1):
+        """ILU0 kernel schedules (see su2b200_linsys_set_schedule); -1 keeps the current one."""
+        check(self.lib.su2b200_linsys_set_schedule(self.ctx, self.which, int(apply_mode), int(build_mode)))
+
     def set_matrix(self, blocks):
         b = as_f64(blocks).ravel()
         assert b.size == self.nnz * self.nVar * self.nVar
