@@ -141,8 +141,14 @@ __global__ void __launch_bounds__(256) k_spmv(int Pd, const int* __restrict__ ro
   double acc = 0.0;
   if (active) {
     for (int k = kb + g; k < ke; k += BPW) {
+#ifdef SPMV_STREAM
+      // matrix entries are used once per product: evict-first, the L2 is kept for the gathered x
+      const int col = __ldcs(col_ind + k);
+      acc += __ldcs(A + (size_t)k * LPB + q) * x[(size_t)col * NV + cc];
+#else
       const int col = col_ind[k];
       acc += A[(size_t)k * LPB + q] * x[(size_t)col * NV + cc];
+#endif
     }
   }
   // reduce over the column index within a block row (lanes q = r*NV .. r*NV+NV-1 are adjacent)

@@ -65,6 +65,12 @@ __global__ void k_fill_sentinel(size_t n, double* __restrict__ a, double* __rest
 // Row t of the level-ordered list belongs to warp t mod W (W = every warp of the co-resident grid), so a warp knows its
 // future rows: while it polls for row t it already holds the matrix entries of row t+W and the descriptor of row t+2W.
 // Only the poll -> fma -> store hop of a row is on the dependency chain.
+// factor entries are read once per sweep: streaming loads (evict-first) leave the L2 to the vector being polled
+#ifdef POLL_STREAM_LOADS
+#define POLL_LD(p) __ldcs(p)
+#else
+#define POLL_LD(p) (*(p))
+#endif
 template <int NV>
 struct RowData {
   static constexpr int CH = 4;  // entries fetched ahead (3 lower/upper neighbours on a hex box, more on tets: tail loop)
@@ -80,8 +86,8 @@ __device__ __forceinline__ void fetch_row(RowData<NV>& d, const int4 m, int q, i
 #pragma unroll
   for (int k = 0; k < RowData<NV>::CH; ++k) {
     const int idx = m.y + k < m.z ? m.y + k : (m.z > m.y ? m.z - 1 : m.y);
-    d.jj[k] = m.z > m.y ? col_ind[idx] : 0;
-    d.a[k] = m.z > m.y ? ILU[(size_t)idx * LPB + q] : 0.0;
+    d.jj[k] = m.z > m.y ? POLL_LD(col_ind + idx) : 0;
+    d.a[k] = m.z > m.y ? POLL_LD(ILU + (size_t)idx * LPB + q) : 0.0;
   }
   d.rhs = in[(size_t)m.x * NV + r];
   d.minv = FORWARD ? 0.0 : invM[(size_t)m.x * LPB + q];
