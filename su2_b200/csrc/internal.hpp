@@ -147,7 +147,9 @@ struct LinSys {
   dvec<int> factor_desc, factor_ops;  // symbolic factorisation: row descriptors (level order) and update lists
   int factor_own_cap = 0, factor_src_cap = 0;
   int factor_slots = 0;               // scalar systems: level-padded row slots of k_factor_poll_s
+  dvec<int> sweep_metar_lower, sweep_metar_upper;  // same, levels padded to 32/nVar rows (k_poll_sweep_rows)
   dvec<int> sweep_meta_lower, sweep_meta_upper;  // int4 {row, first, last+1, 0} per level-ordered position (mode 2)
+  int poll_split_lower[4] = {0, 0, 0, 0}, poll_split_upper[4] = {0, 0, 0, 0};  // hybrid sweep: see build_meta
   int poll_groups_lower = 0, poll_groups_upper = 0;  // scalar systems: groups of 4 level-padded rows
   dvec<double> sweep_tmp, sweep_tmp2;  // forward-sweep result / copy of an in-place rhs (mode 2)
   // reference-style row partitions (block-Jacobi ILU across partitions); nparts <= 1: exact serial factor

@@ -126,6 +126,9 @@ double vec_dot(su2b200_ctx* c, LinSys& ls, const double* a, const double* b) {
 // ------------------------------------------------------------------------------------------------
 // SpMV: one warp per block-row.
 // ------------------------------------------------------------------------------------------------
+#ifndef SPMV_UNROLL
+#define SPMV_UNROLL 1
+#endif
 template <int NV>
 __global__ void __launch_bounds__(256) k_spmv(int Pd, const int* __restrict__ row_ptr, const int* __restrict__ col_ind,
                                               const double* __restrict__ A, const double* __restrict__ x,
@@ -140,7 +143,26 @@ __global__ void __launch_bounds__(256) k_spmv(int Pd, const int* __restrict__ ro
   const int kb = row_ptr[warp], ke = row_ptr[warp + 1];
   double acc = 0.0;
   if (active) {
+#if SPMV_UNROLL > 1
+    // SPMV_UNROLL entries per trip with all their loads issued before the first use: twice (or four times) the bytes in
+    // flight per warp; the accumulation order is unchanged
+    int k = kb + g;
+    for (; k + (SPMV_UNROLL - 1) * BPW < ke; k += SPMV_UNROLL * BPW) {
+      int col[SPMV_UNROLL];
+      double a[SPMV_UNROLL], xv[SPMV_UNROLL];
+#pragma unroll
+      for (int u = 0; u < SPMV_UNROLL; ++u) col[u] = col_ind[k + u * BPW];
+#pragma unroll
+      for (int u = 0; u < SPMV_UNROLL; ++u) a[u] = A[(size_t)(k + u * BPW) * LPB + q];
+#pragma unroll
+      for (int u = 0; u < SPMV_UNROLL; ++u) xv[u] = x[(size_t)col[u] * NV + cc];
+#pragma unroll
+      for (int u = 0; u < SPMV_UNROLL; ++u) acc += a[u] * xv[u];
+    }
+    for (; k < ke; k += BPW) {
+#else
     for (int k = kb + g; k < ke; k += BPW) {
+#endif
 #ifdef SPMV_STREAM
       // matrix entries are used once per product: evict-first, the L2 is kept for the gathered x
       const int col = __ldcs(col_ind + k);

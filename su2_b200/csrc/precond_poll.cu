@@ -119,15 +119,24 @@ __global__ void __launch_bounds__(128) k_poll_sweep(int n, const int4* __restric
 #pragma unroll
     for (int k = 0; k < CH; ++k)  // all first looks in flight together: one L2 round trip when the row is ready
       yv[k] = kb + k < ke ? ld_relaxed(out + (size_t)cur.jj[k] * NV + cc) : 0.0;
+    // whatever is missing is looked at again, all of it per round (one L2 round trip per round, not per dependency)
+    for (unsigned spins = 0;; ++spins) {
+      bool miss = false;
 #pragma unroll
-    for (int k = 0; k < CH; ++k) {
-      if (kb + k < ke) {
-        if ((unsigned long long)__double_as_longlong(yv[k]) == SENTINEL &&
-            !poll(out + (size_t)cur.jj[k] * NV + cc, ctrl, yv[k]))
-          return;  // watchdog
-        acc += cur.a[k] * yv[k];
+      for (int k = 0; k < CH; ++k)
+        if ((unsigned long long)__double_as_longlong(yv[k]) == SENTINEL) {
+          miss = true;
+          yv[k] = ld_relaxed(out + (size_t)cur.jj[k] * NV + cc);
+        }
+      if (!__any_sync(FULLM, miss)) break;
+      if ((spins & 1023u) == 1023u) {
+        if (spins > (1u << 22)) atomicExch(ctrl + 1, 1);
+        if (ld_relaxed_i(ctrl + 1) != 0) return;  // watchdog (warp-uniform: the vote above keeps the lanes together)
       }
     }
+#pragma unroll
+    for (int k = 0; k < CH; ++k)
+      if (kb + k < ke) acc += cur.a[k] * yv[k];
     for (int idx = kb + CH; idx < ke; ++idx) {  // rows with more than CH entries on this side
       const int j = col_ind[idx];
       const double a = ILU[(size_t)idx * LPB + q];
@@ -152,6 +161,235 @@ __global__ void __launch_bounds__(128) k_poll_sweep(int n, const int4* __restric
     cur = nxt;
     m_cur = m_nxt;
     m_nxt = m_nn;
+  }
+}
+
+// ---- the same sweep with a deeper, shared-memory pipeline --------------------------------------------------------------
+// In the wide levels every row is ready when its warp reaches it and the sweep is bound by how many bytes of the factor
+// are in flight: with a one-row register prefetch a warp waits for DRAM at every row. Here the entries, columns, rhs and
+// inverse diagonal of the next PIPE-1 rows are streamed into a ring of PIPE shared-memory stages with cp.async.
+static constexpr int PIPE = 4;
+template <int NV>
+struct SweepStage {  // one row
+  static constexpr int CH = 4;
+  double a[CH][NV * NV];
+  double minv[NV * NV];
+  double rhs[NV];
+  int col[CH];
+};
+__device__ __forceinline__ void cp_async_8(void* smem, const void* gmem) {
+  const unsigned s = (unsigned)__cvta_generic_to_shared(smem);
+  asm volatile("cp.async.ca.shared.global [%0], [%1], 8;" ::"r"(s), "l"(gmem) : "memory");
+}
+__device__ __forceinline__ void cp_async_4(void* smem, const void* gmem) {
+  const unsigned s = (unsigned)__cvta_generic_to_shared(smem);
+  asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"(s), "l"(gmem) : "memory");
+}
+
+template <int NV, bool FORWARD>
+__global__ void __launch_bounds__(128) k_poll_sweep_pipe(int n, const int4* __restrict__ meta, int* ctrl,
+                                                         const int* __restrict__ col_ind, const double* __restrict__ ILU,
+                                                         const double* __restrict__ invM, const double* __restrict__ in,
+                                                         double* out) {
+  constexpr int LPB = NV * NV;
+  constexpr int CH = SweepStage<NV>::CH;
+  extern __shared__ double smem_raw[];
+  SweepStage<NV>* ring = reinterpret_cast<SweepStage<NV>*>(smem_raw) + (threadIdx.x >> 5) * PIPE;
+  const int lane = threadIdx.x & 31;
+  const int q = lane < LPB ? lane : LPB - 1;
+  const int r = q / NV, cc = q % NV;
+  const int W = gridDim.x * (blockDim.x >> 5);
+  int t = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
+  if (t >= n) return;
+
+  auto stage = [&](const int4 m, SweepStage<NV>& s) {
+    if (lane < LPB) {
+#pragma unroll
+      for (int k = 0; k < CH; ++k)
+        if (m.y + k < m.z) cp_async_8(&s.a[k][lane], ILU + (size_t)(m.y + k) * LPB + lane);
+      if (!FORWARD) cp_async_8(&s.minv[lane], invM + (size_t)m.x * LPB + lane);
+    }
+    if (lane < NV) cp_async_8(&s.rhs[lane], in + (size_t)m.x * NV + lane);
+    if (lane < CH && m.y + lane < m.z) cp_async_4(&s.col[lane], col_ind + m.y + lane);
+    asm volatile("cp.async.commit_group;" ::: "memory");
+  };
+
+  // descriptors PIPE rows ahead, data PIPE-1 rows ahead
+  int4 m[PIPE];
+#pragma unroll
+  for (int p = 0; p < PIPE; ++p) m[p] = t + p * W < n ? meta[t + p * W] : make_int4(0, 0, 0, 0);
+#pragma unroll
+  for (int p = 0; p < PIPE - 1; ++p) {
+    if (t + p * W < n) stage(m[p], ring[p]);
+    else asm volatile("cp.async.commit_group;" ::: "memory");
+  }
+  int slot = 0;
+  // first looks at the dependencies are issued one row ahead as well: in the wide levels the values are there long
+  // before the warp arrives, and the L2 round trip of the look would otherwise be paid once per row per warp
+  double yv[CH], yvN[CH];
+  int jj[CH], jjN[CH];
+  auto look = [&](const int4 mm, const SweepStage<NV>& s, int (&cols)[CH], double (&vals)[CH]) {
+#pragma unroll
+    for (int k = 0; k < CH; ++k) {
+      cols[k] = mm.y + k < mm.z ? s.col[k] : 0;
+      vals[k] = mm.y + k < mm.z ? ld_relaxed(out + (size_t)cols[k] * NV + cc) : 0.0;
+    }
+  };
+  asm volatile("cp.async.wait_group %0;" ::"n"(PIPE - 2) : "memory");
+  __syncwarp();
+  look(m[0], ring[0], jj, yv);
+  for (; t < n; t += W) {
+    const int4 m_new = t + PIPE * W < n ? meta[t + PIPE * W] : make_int4(0, 0, 0, 0);
+    if (t + (PIPE - 1) * W < n) stage(m[PIPE - 1], ring[(slot + PIPE - 1) % PIPE]);
+    else asm volatile("cp.async.commit_group;" ::: "memory");
+    asm volatile("cp.async.wait_group %0;" ::"n"(PIPE - 2) : "memory");  // stages of this row and of the next one
+    __syncwarp();
+    if (t + W < n) look(m[1], ring[(slot + 1) % PIPE], jjN, yvN);
+    const SweepStage<NV>& s = ring[slot];
+    const int i = m[0].x, kb = m[0].y, ke = m[0].z;
+    double acc = 0.0;
+#pragma unroll
+    for (int k = 0; k < CH; ++k) {
+      if (kb + k < ke) {
+        if ((unsigned long long)__double_as_longlong(yv[k]) == SENTINEL &&
+            !poll(out + (size_t)jj[k] * NV + cc, ctrl, yv[k]))
+          return;  // watchdog
+        acc += s.a[k][q] * yv[k];
+      }
+    }
+    for (int idx = kb + CH; idx < ke; ++idx) {  // rows with more than CH entries on this side
+      const int j = col_ind[idx];
+      const double a = ILU[(size_t)idx * LPB + q];
+      double yj;
+      if (!poll(out + (size_t)j * NV + cc, ctrl, yj)) return;
+      acc += a * yj;
+    }
+    double sum = acc;
+#pragma unroll
+    for (int o = 1; o < NV; ++o) sum += __shfl_down_sync(FULLM, acc, o);
+    const double rhs = s.rhs[r];
+    if (FORWARD) {
+      if (lane < LPB && cc == 0) st_relaxed(out + (size_t)i * NV + r, rhs - sum);
+    } else {
+      const double aux_r = rhs - sum;  // valid on lanes r*NV
+      const double aux_c = __shfl_sync(FULLM, aux_r, cc * NV);
+      const double prod = s.minv[q] * aux_c;
+      double tsum = prod;
+#pragma unroll
+      for (int o = 1; o < NV; ++o) tsum += __shfl_down_sync(FULLM, prod, o);
+      if (lane < LPB && cc == 0) st_relaxed(out + (size_t)i * NV + r, tsum);
+    }
+    __syncwarp();  // every lane is done with this stage before it is refilled
+#pragma unroll
+    for (int p = 0; p < PIPE - 1; ++p) m[p] = m[p + 1];
+    m[PIPE - 1] = m_new;
+    slot = (slot + 1) % PIPE;
+#pragma unroll
+    for (int k = 0; k < CH; ++k) { yv[k] = yvN[k]; jj[k] = jjN[k]; }
+  }
+}
+
+// ---- block systems, nVar lanes per row ----------------------------------------------------------------------------------
+// ncu showed the warp-per-row sweeps to be bound by instruction issue in the wide levels (every resident warp has a
+// ready row; ~210 warp instructions per row, 25 of 32 lanes busy). Here lane r of a group of nVar lanes owns block row
+// r: it loads the nVar entries of its row of each block (the group reads the 200 contiguous bytes of the block), the
+// nVar values of the dependency, and accumulates exactly as the reference does (product of block and vector summed
+// over the column, then subtracted from the row). 32/nVar rows per warp and ~30 warp instructions per row. The rows of
+// a warp belong to one level (levels padded), so they never wait for one another.
+#ifndef ROWS_CH
+#define ROWS_CH 3
+#endif
+#ifndef ROWS_MIN_BLOCKS
+#define ROWS_MIN_BLOCKS 5
+#endif
+template <int NV, bool FORWARD>
+__global__ void __launch_bounds__(128, ROWS_MIN_BLOCKS) k_poll_sweep_rows(int nGroups, const int4* __restrict__ meta, int* ctrl,
+                                                         const int* __restrict__ col_ind, const double* __restrict__ ILU,
+                                                         const double* __restrict__ invM, const double* __restrict__ in,
+                                                         double* out) {
+  constexpr int LPB = NV * NV;
+  constexpr int RPW = 32 / NV;  // rows per warp
+  constexpr int CH = ROWS_CH;   // entries held in registers (a hex row has 3 on each side); longer rows: tail loop
+  const int lane = threadIdx.x & 31;
+  const int sub = lane / NV, r = lane % NV;
+  const bool live = sub < RPW;
+  const int W = gridDim.x * (blockDim.x >> 5);
+  bool ok = true;  // after the watchdog fired the lanes idle through their remaining rows (shuffles need them all)
+  for (int g = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5); g < nGroups; g += W) {
+    const int4 m = live ? meta[(size_t)g * RPW + sub] : make_int4(-1, 0, 0, 0);
+    const int i = m.x, kb = m.y, ke = m.z;
+    const bool on = ok && i >= 0;
+    // everything that does not depend on the sweep first: columns, block rows, rhs (and the inverse diagonal)
+    int jj[CH];
+    double a[CH][NV];
+#pragma unroll
+    for (int k = 0; k < CH; ++k) {
+      const bool has = on && kb + k < ke;
+      jj[k] = has ? col_ind[kb + k] : 0;
+#pragma unroll
+      for (int c = 0; c < NV; ++c) a[k][c] = has ? ILU[(size_t)(kb + k) * LPB + r * NV + c] : 0.0;
+    }
+    double v = on ? in[(size_t)i * NV + r] : 0.0;
+    double dinv[NV];
+    if (!FORWARD) {
+#pragma unroll
+      for (int c = 0; c < NV; ++c) dinv[c] = on ? invM[(size_t)i * LPB + r * NV + c] : 0.0;
+    }
+    // first look at every dependency, then wait only for what is missing
+    double y[CH][NV];
+#pragma unroll
+    for (int k = 0; k < CH; ++k)
+#pragma unroll
+      for (int c = 0; c < NV; ++c)
+        y[k][c] = (on && kb + k < ke) ? ld_relaxed(out + (size_t)jj[k] * NV + c) : 0.0;
+    // whatever is still missing is looked at again, all of it per round (one L2 round trip per round, not per value)
+    for (unsigned spins = 0;; ++spins) {
+      bool miss = false;
+#pragma unroll
+      for (int k = 0; k < CH; ++k)
+#pragma unroll
+        for (int c = 0; c < NV; ++c)
+          if ((unsigned long long)__double_as_longlong(y[k][c]) == SENTINEL) {
+            miss = true;
+            y[k][c] = ld_relaxed(out + (size_t)jj[k] * NV + c);
+          }
+      if (!miss) break;
+      if ((spins & 1023u) == 1023u) {
+        if (spins > (1u << 22)) atomicExch(ctrl + 1, 1);
+        if (ld_relaxed_i(ctrl + 1) != 0) { ok = false; break; }
+      }
+    }
+#pragma unroll
+    for (int k = 0; k < CH; ++k) {
+      if (on && ok && kb + k < ke) {
+        double p = 0.0;
+#pragma unroll
+        for (int c = 0; c < NV; ++c) p += a[k][c] * y[k][c];
+        v -= p;
+      }
+    }
+    if (on) {
+      for (int idx = kb + CH; idx < ke && ok; ++idx) {  // rows with more than CH entries on this side
+        const int j = col_ind[idx];
+        double p = 0.0;
+        for (int c = 0; c < NV && ok; ++c) {
+          double yj;
+          ok = poll(out + (size_t)j * NV + c, ctrl, yj);
+          p += ILU[(size_t)idx * LPB + r * NV + c] * yj;
+        }
+        v -= p;
+      }
+    }
+    if (FORWARD) {
+      if (on && ok) st_relaxed(out + (size_t)i * NV + r, v);
+    } else {
+      // x_i = invM_i * aux (MatrixVectorProduct): lane r needs the whole aux vector of its row
+      double x = 0.0;
+#pragma unroll
+      for (int c = 0; c < NV; ++c) x += dinv[c] * __shfl_sync(FULLM, v, sub * NV + c);
+      if (on && ok) st_relaxed(out + (size_t)i * NV + r, x);
+    }
+    ok = __all_sync(FULLM, ok);
   }
 }
 
@@ -213,16 +451,22 @@ __global__ void __launch_bounds__(128) k_poll_sweep_s(int nGroups, const int4* _
 // Every warp of the grid must be resident (rows are assigned round-robin and a warp may wait for any smaller row):
 // cooperative launch makes the driver enforce that, the occupancy query sizes the grid.
 template <class K, class... Args>
-static void launch_resident(su2b200_ctx* c, K kernel, int maxBlocksUseful, int blocksPerSmCap, Args... args) {
+static void launch_resident_smem(su2b200_ctx* c, K kernel, size_t smem, int maxBlocksUseful, int blocksPerSmCap,
+                                 Args... args) {
   int dev = 0, nsm = 0, perSm = 0;
   SU2B_CUDA(cudaGetDevice(&dev));
   SU2B_CUDA(cudaDeviceGetAttribute(&nsm, cudaDevAttrMultiProcessorCount, dev));
-  SU2B_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&perSm, kernel, 128, 0));
+  SU2B_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&perSm, kernel, 128, smem));
+  SU2B_REQUIRE(perSm > 0, "sweep kernel does not fit an SM");
   if (blocksPerSmCap > 0) perSm = std::min(perSm, blocksPerSmCap);
   const int grid = std::max(1, std::min(maxBlocksUseful, nsm * perSm));
   void* argv[] = {(void*)&args...};
-  SU2B_CUDA(cudaLaunchCooperativeKernel((const void*)kernel, dim3(grid), dim3(128), argv, 0, c->stream));
+  SU2B_CUDA(cudaLaunchCooperativeKernel((const void*)kernel, dim3(grid), dim3(128), argv, smem, c->stream));
   c->launches++;
+}
+template <class K, class... Args>
+static void launch_resident(su2b200_ctx* c, K kernel, int maxBlocksUseful, int blocksPerSmCap, Args... args) {
+  launch_resident_smem(c, kernel, 0, maxBlocksUseful, blocksPerSmCap, args...);
 }
 
 // level-ordered row descriptors {row, first entry, one past the last entry on this side of the diagonal, 0}
@@ -265,6 +509,40 @@ static void build_meta(LinSys& ls) {
   } else {
     make(ls.lvl_rows_lower.to_host(), true, ls.sweep_meta_lower);
     make(ls.lvl_rows_upper.to_host(), false, ls.sweep_meta_upper);
+    // k_poll_sweep_rows: 32/nVar rows per warp, every level padded to that
+    const int rpw = 32 / ls.nVar;
+    auto pad = [&](const std::vector<int>& ptr, const std::vector<int>& rows, int& groups) {
+      std::vector<int> p;
+      p.reserve(rows.size() + (size_t)rpw * ptr.size());
+      for (size_t l = 0; l + 1 < ptr.size(); ++l) {
+        for (int k = ptr[l]; k < ptr[l + 1]; ++k) p.push_back(rows[k]);
+        while (p.size() % rpw) p.push_back(-1);
+      }
+      groups = (int)(p.size() / rpw);
+      return p;
+    };
+    make(pad(ls.lvl_ptr_lower, ls.lvl_rows_lower.to_host(), ls.poll_groups_lower), true, ls.sweep_metar_lower);
+    make(pad(ls.lvl_ptr_upper, ls.lvl_rows_upper.to_host(), ls.poll_groups_upper), false, ls.sweep_metar_upper);
+    // hybrid schedule: the contiguous run of wide levels [first, last] goes to the rows kernel, the narrow head and tail
+    // to the warp-per-row kernel. split = {rows before the run, groups before the run, rows at its end, groups at its end}
+    // (185^3, ms per application: threshold 1024 -> 3.75, 4096 -> 3.53, 16384 -> 3.46; warp-per-row only 3.97)
+    const int wide = getenv("SU2B200_SWEEP_WIDE") ? atoi(getenv("SU2B200_SWEEP_WIDE")) : 16384;
+    auto split = [&](const std::vector<int>& ptr, int (&sp)[4]) {
+      const int nl = (int)ptr.size() - 1;
+      int first = -1, last = -1;
+      for (int l = 0; l < nl; ++l)
+        if (ptr[l + 1] - ptr[l] >= wide) { if (first < 0) first = l; last = l; }
+      auto groups_before = [&](int lev) {
+        long g = 0;
+        for (int l = 0; l < lev; ++l) g += (ptr[l + 1] - ptr[l] + rpw - 1) / rpw;
+        return (int)g;
+      };
+      if (first < 0) { sp[0] = sp[2] = ptr[nl]; sp[1] = sp[3] = groups_before(nl); return; }
+      sp[0] = ptr[first]; sp[1] = groups_before(first);
+      sp[2] = ptr[last + 1]; sp[3] = groups_before(last + 1);
+    };
+    split(ls.lvl_ptr_lower, ls.poll_split_lower);
+    split(ls.lvl_ptr_upper, ls.poll_split_upper);
   }
 }
 
@@ -289,8 +567,37 @@ static void ilu_apply_poll_impl(su2b200_ctx* c, LinSys& ls, const double* x, dou
     launch_resident(c, k_poll_sweep_s<false>, (ls.poll_groups_upper + 3) / 4, capS, ls.poll_groups_upper, mu, ctrl, ci, ilu, invM,
                     (const double*)w, y);
   } else {
-    launch_resident(c, k_poll_sweep<NV, true>, (ls.Pd + 3) / 4, capB, ls.Pd, ml, ctrl, ci, ilu, invM, x, w);
-    launch_resident(c, k_poll_sweep<NV, false>, (ls.Pd + 3) / 4, capB, ls.Pd, mu, ctrl, ci, ilu, invM, (const double*)w, y);
+    // 2: nVar lanes per row (default); 1: warp per row with the shared-memory pipeline; 0: warp per row, register prefetch
+    static const int pipe = getenv("SU2B200_SWEEP_PIPE") ? atoi(getenv("SU2B200_SWEEP_PIPE")) : 2;
+    if (pipe == 2) {
+      // hybrid: narrow levels (bound by the hop from level to level: 0.8 us with a warp per row, 2 us with 32/nVar
+      // coupled rows per warp) -> k_poll_sweep; wide levels (bound by instruction issue: 210 vs 30 warp instructions
+      // per row) -> k_poll_sweep_rows. Up to three launches per sweep, split at level boundaries.
+      const int4* mrl = reinterpret_cast<const int4*>(ls.sweep_metar_lower.p);
+      const int4* mru = reinterpret_cast<const int4*>(ls.sweep_metar_upper.p);
+      auto sweep = [&](auto narrowK, auto wideK, const int4* mnar, const int4* mwid, const int (&sp)[4], int nGroups,
+                       const double* src, double* dst) {
+        const int nRows = ls.Pd;
+        if (sp[0] > 0) launch_resident(c, narrowK, (sp[0] + 3) / 4, capB, sp[0], mnar, ctrl, ci, ilu, invM, src, dst);
+        if (sp[3] > sp[1])
+          launch_resident(c, wideK, (sp[3] - sp[1] + 3) / 4, 0, sp[3] - sp[1], mwid + (size_t)sp[1] * (32 / NV), ctrl, ci,
+                          ilu, invM, src, dst);
+        if (nRows > sp[2])
+          launch_resident(c, narrowK, (nRows - sp[2] + 3) / 4, capB, nRows - sp[2], mnar + sp[2], ctrl, ci, ilu, invM, src, dst);
+        (void)nGroups;
+      };
+      sweep(k_poll_sweep<NV, true>, k_poll_sweep_rows<NV, true>, ml, mrl, ls.poll_split_lower, ls.poll_groups_lower, x, w);
+      sweep(k_poll_sweep<NV, false>, k_poll_sweep_rows<NV, false>, mu, mru, ls.poll_split_upper, ls.poll_groups_upper,
+            (const double*)w, y);
+    } else if (pipe) {
+      const size_t smem = (size_t)4 * PIPE * sizeof(SweepStage<NV>);
+      launch_resident_smem(c, k_poll_sweep_pipe<NV, true>, smem, (ls.Pd + 3) / 4, capB, ls.Pd, ml, ctrl, ci, ilu, invM, x, w);
+      launch_resident_smem(c, k_poll_sweep_pipe<NV, false>, smem, (ls.Pd + 3) / 4, capB, ls.Pd, mu, ctrl, ci, ilu, invM,
+                           (const double*)w, y);
+    } else {
+      launch_resident(c, k_poll_sweep<NV, true>, (ls.Pd + 3) / 4, capB, ls.Pd, ml, ctrl, ci, ilu, invM, x, w);
+      launch_resident(c, k_poll_sweep<NV, false>, (ls.Pd + 3) / 4, capB, ls.Pd, mu, ctrl, ci, ilu, invM, (const double*)w, y);
+    }
   }
 }
 
