@@ -146,6 +146,10 @@ struct LinSys {
   bool factor_ready = false, factor_ok = false;
   dvec<int> factor_desc, factor_ops;  // symbolic factorisation: row descriptors (level order) and update lists
   int factor_own_cap = 0, factor_src_cap = 0;
+  bool factor_rows_ok = false;        // every row fits k_factor_rows' tiles
+  int factor_groups = 0;              // groups of 32/nVar level-padded rows (k_factor_rows)
+  dvec<int> factor_desc_rows;
+  int factor_split[4] = {0, 0, 0, 0};  // wide middle: level-ordered rows [0],[1]) = padded groups [2],[3])
   int factor_slots = 0;               // scalar systems: level-padded row slots of k_factor_poll_s
   dvec<int> sweep_metar_lower, sweep_metar_upper;  // same, levels padded to 32/nVar rows (k_poll_sweep_rows)
   dvec<int> sweep_meta_lower, sweep_meta_upper;  // int4 {row, first, last+1, 0} per level-ordered position (mode 2)

@@ -355,6 +355,245 @@ __global__ void __launch_bounds__(128) k_factor_poll_s(int nSlots, const RowDesc
   }
 }
 
+// ---- block systems, nVar lanes per matrix row ---------------------------------------------------------------------------
+// k_factor_poll spends ~1500 warp instructions per row, most of them shuffles and index arithmetic of the
+// one-scalar-per-lane products (ncu: issue-bound, 6 % of its instructions are DFMA). Here lane r of a group of nVar
+// lanes owns block row r of every block of its matrix row; the blocks live in shared-memory tiles (own row, staged
+// stable sources, the current inverse diagonal), products read their second operand from the tile (no shuffles), the
+// Gauss inversion exchanges pivot rows inside the group. 32/nVar matrix rows per warp, ~100 warp instructions per row.
+// Same arithmetic, element by element, as CSysMatrix.cpp:714-760 / MatrixInverse :548-601.
+static constexpr int RF_OWN = 8;   // most blocks of a row (longer rows: k_factor_poll handles the matrix); tiles follow the matrix
+static constexpr int RF_SRC = 4;   // stable sources staged with the row (others are read when needed)
+static constexpr int RF_LOW = 4;   // lower neighbours whose inverse diagonal is looked at ahead
+
+__device__ __forceinline__ bool is_sentinel(double v) {
+  // every double with this high word is a NaN that arithmetic cannot produce: the high word identifies the sentinel
+  return (unsigned)__double2hiint(v) == (unsigned)(SENTINEL >> 32);
+}
+
+template <int NV>
+__global__ void __launch_bounds__(128) k_factor_rows(int nGroups, int ownCap, int srcCap, const RowDesc* __restrict__ desc,
+                                                     const int2* __restrict__ ops, int* ctrl,
+                                                     const int* __restrict__ col_ind, const double* __restrict__ A,
+                                                     double* ILU, double* invM) {
+  constexpr int LPB = NV * NV;
+  constexpr int RPW = 32 / NV;
+  const int TILES = ownCap + srcCap + 1;  // own row, staged stable sources, the inverse diagonal in use
+  extern __shared__ double smem[];
+  const int lane = threadIdx.x & 31, wib = threadIdx.x >> 5;
+  const int sub = lane / NV, r = lane % NV;
+  const bool live = sub < RPW;
+  const unsigned gmask = live ? (((1u << NV) - 1u) << (sub * NV))
+                              : (RPW * NV < 32 ? (0xffffffffu << ((RPW * NV) & 31)) : 0u);
+  double* T = smem + (size_t)((wib * RPW + (live ? sub : 0)) * TILES) * LPB;
+  double* invT = T + (size_t)(ownCap + srcCap) * LPB;
+  const int W = gridDim.x * (blockDim.x >> 5);
+  bool ok = true;
+  // descriptors run two groups ahead so that the rows of the next group can be pulled into L2 while this one works
+  RowDesc d1, d2;
+  d1.a = d2.a = make_int4(-1, 0, 0, 0);
+  d1.b = d2.b = make_int4(0, 0, 0, 0);
+  const int g0 = blockIdx.x * (blockDim.x >> 5) + wib;
+  if (live && g0 < nGroups) d1 = desc[(size_t)g0 * RPW + sub];
+  if (live && g0 + W < nGroups) d2 = desc[(size_t)(g0 + W) * RPW + sub];
+  for (int g = g0; g < nGroups; g += W) {
+    const RowDesc d = d1;
+    d1 = d2;
+    d2.a = make_int4(-1, 0, 0, 0);
+    d2.b = make_int4(0, 0, 0, 0);
+    if (live && g + 2 * W < nGroups) d2 = desc[(size_t)(g + 2 * W) * RPW + sub];
+    if (d1.a.x >= 0) {
+      const char* nb = reinterpret_cast<const char*>(A + (size_t)d1.a.y * LPB);
+      const int bytes = (d1.a.w - d1.a.y) * LPB * (int)sizeof(double);
+      for (int off = r * 128; off < bytes; off += NV * 128) asm volatile("prefetch.global.L2 [%0];" ::"l"(nb + off));
+      if (r == 0) asm volatile("prefetch.global.L2 [%0];" ::"l"(col_ind + d1.a.y));
+      if (r == 1 && d1.b.y > 0) asm volatile("prefetch.global.L2 [%0];" ::"l"(ops + d1.b.x));
+    }
+    const int i = d.a.x, rb = d.a.y, di = d.a.z, re = d.a.w;
+    const bool on = ok && i >= 0;
+    const int nOwn = on ? re - rb : 0, nl = on ? di - rb : 0, nOps = on ? d.b.y : 0;
+    // the row itself (asynchronous copies into its tiles), the first update ops and the columns of the lower entries
+    // in one round of loads, then the first look at the awaited inverse diagonals (row r of each) and the staged
+    // sources: three dependent rounds of memory latency per group instead of one per array
+    for (int s = 0; s < nOwn; ++s)
+#pragma unroll
+      for (int c = 0; c < NV; ++c) cp_async8(T + s * LPB + r * NV + c, A + (size_t)(rb + s) * LPB + r * NV + c);
+    int2 opr[RF_SRC];
+#pragma unroll
+    for (int k = 0; k < RF_SRC; ++k) opr[k] = k < nOps ? ops[d.b.x + k] : make_int2(0, 0);
+    int col[RF_LOW];
+#pragma unroll
+    for (int s = 0; s < RF_LOW; ++s) col[s] = s < nl ? col_ind[rb + s] : 0;
+    double look[RF_LOW][NV];
+#pragma unroll
+    for (int s = 0; s < RF_LOW; ++s) {
+#pragma unroll
+      for (int c = 0; c < NV; ++c) look[s][c] = s < nl ? ldr(invM + (size_t)col[s] * LPB + r * NV + c) : 0.0;
+    }
+#pragma unroll
+    for (int k = 0; k < RF_SRC; ++k) {
+      const unsigned sidx = (unsigned)opr[k].x;
+      if (k < min(nOps, srcCap) && (sidx & STABLE)) {
+#pragma unroll
+        for (int c = 0; c < NV; ++c)
+          cp_async8(T + (ownCap + k) * LPB + r * NV + c, A + (size_t)(sidx & ~STABLE) * LPB + r * NV + c);
+      }
+    }
+    cp_async_commit();
+    cp_async_wait<0>();
+    __syncwarp();
+    int u = 0;
+    // the matrix rows of a warp walk their lower entries in lockstep (one converged instruction stream: divergent
+    // per-row poll loops share the warp's scoreboard and serialise, measured 40 us per level)
+    const int nlMax = __reduce_max_sync(FULLM, nl);
+    for (int s = 0; s < nlMax; ++s) {
+      const bool act = s < nl;
+      // inverse diagonal of neighbour j: row r of it, re-polled until complete
+      double inv[NV];
+      int jcol = (act && s >= RF_LOW) ? col_ind[rb + s] : 0;
+#pragma unroll
+      for (int c = 0; c < NV; ++c) inv[c] = act ? __longlong_as_double((long long)SENTINEL) : 0.0;
+#pragma unroll
+      for (int k = 0; k < RF_LOW; ++k)
+        if (s == k) {
+          jcol = col[k];
+#pragma unroll
+          for (int c = 0; c < NV; ++c) inv[c] = act ? look[k][c] : 0.0;
+        }
+      const double* pin = invM + (size_t)jcol * LPB + r * NV;
+      // the lanes of a row watch ONE element of the awaited block (a single sector per row and round: 1776 warps
+      // re-reading whole blocks saturate the L2 and slow the rows that everybody waits for), then fetch their own
+      const double* plast = invM + (size_t)jcol * LPB + (LPB - 1);
+      for (unsigned spins = 0;; ++spins) {
+        bool miss = false;
+#pragma unroll
+        for (int c = 0; c < NV; ++c) miss = miss || is_sentinel(inv[c]);
+        if (!__any_sync(FULLM, miss)) break;
+        if (miss && !is_sentinel(ldr(plast))) {
+#pragma unroll
+          for (int c = 0; c < NV; ++c)
+            if (is_sentinel(inv[c])) inv[c] = ldr(pin + c);
+        }
+        if ((spins & 1023u) == 1023u) {
+          if (spins > (1u << 22)) atomicExch(ctrl + 1, 1);
+          if (__any_sync(FULLM, ldr_i(ctrl + 1) != 0)) { ok = false; break; }
+        }
+      }
+      if (!ok) break;
+      if (act) {
+#pragma unroll
+        for (int c = 0; c < NV; ++c) invT[r * NV + c] = inv[c];
+      }
+      __syncwarp();
+      // w = A_ij * inv(U_jj): row r
+      double w[NV];
+#pragma unroll
+      for (int c = 0; c < NV; ++c) w[c] = 0.0;
+      if (act) {
+        double a[NV];
+#pragma unroll
+        for (int m = 0; m < NV; ++m) a[m] = T[s * LPB + r * NV + m];
+#pragma unroll
+        for (int c = 0; c < NV; ++c) {
+          double acc = 0.0;
+#pragma unroll
+          for (int m = 0; m < NV; ++m) acc += a[m] * invT[m * NV + c];
+          w[c] = acc;
+        }
+      }
+      // A_ik -= w * U_jk for the entries k of row j that meet the pattern of row i
+      bool fenced = false;
+      for (;;) {
+        bool has = act && u < nOps;
+        int2 op = make_int2(0, 0);
+        if (has) {
+          if (u >= RF_SRC) op = ops[d.b.x + u];
+#pragma unroll
+          for (int k = 0; k < RF_SRC; ++k)
+            if (u == k) op = opr[k];
+          has = (op.y >> 16) == s;
+        }
+        if (!__any_sync(FULLM, has)) break;
+        if (has) {
+          const unsigned sidx = (unsigned)op.x;
+          const double* sp;
+          if ((sidx & STABLE) && u < srcCap) sp = T + (size_t)(ownCap + u) * LPB;
+          else if (sidx & STABLE) sp = A + (size_t)(sidx & ~STABLE) * LPB;
+          else {
+            if (!fenced) { __threadfence(); fenced = true; }
+            sp = ILU + (size_t)sidx * LPB;
+          }
+          const bool from_ilu = !(sidx & STABLE);
+          double* tgt = T + (size_t)(op.y & 0xffff) * LPB + r * NV;
+#pragma unroll
+          for (int c = 0; c < NV; ++c) {
+            double acc = 0.0;
+#pragma unroll
+            for (int m = 0; m < NV; ++m) acc += w[m] * (from_ilu ? ldr(sp + m * NV + c) : sp[m * NV + c]);
+            tgt[c] -= acc;
+          }
+          ++u;
+        }
+      }
+      if (act) {
+#pragma unroll
+        for (int c = 0; c < NV; ++c) T[s * LPB + r * NV + c] = w[c];
+      }
+      __syncwarp();  // invT is rewritten by the next lower entry
+    }
+    __syncwarp();
+    // inverse of the factored diagonal block: lane r holds row r of A and of the inverse, pivot rows come by shuffle
+    // lane r holds ROW r of the block being eliminated and COLUMN r of the inverse being built: the elimination
+    // weights (one division per lane and pivot) and the pivot rows travel by shuffle, every update of the inverse is
+    // then local to the lane that owns the column, and the closing divisions run on all columns at once
+    double ar[NV], mc[NV];
+#pragma unroll
+    for (int c = 0; c < NV; ++c) { ar[c] = (on && ok) ? T[nl * LPB + r * NV + c] : (r == c ? 1.0 : 0.0); mc[c] = (r == c) ? 1.0 : 0.0; }
+    const int gbase = sub * NV;
+#pragma unroll
+    for (int jp = 0; jp < NV - 1; ++jp) {
+      double prow[NV];
+#pragma unroll
+      for (int c = jp; c < NV; ++c) prow[c] = __shfl_sync(FULLM, ar[c], gbase + jp);
+      double pj = prow[jp];
+      fix_pivot(pj);
+      if (r == jp) ar[jp] = pj;
+      double wgt = 0.0;
+      if (r > jp) {
+        wgt = ar[jp] / pj;
+#pragma unroll
+        for (int c = jp; c < NV; ++c) ar[c] -= wgt * (c == jp ? pj : prow[c]);
+      }
+#pragma unroll
+      for (int m = jp + 1; m < NV; ++m) {
+        const double wm = __shfl_sync(FULLM, wgt, gbase + m);
+        if (r <= jp) mc[m] -= wm * mc[jp];
+      }
+    }
+#pragma unroll
+    for (int ip = NV - 1; ip >= 0; --ip) {
+#pragma unroll
+      for (int jp = ip + 1; jp < NV; ++jp) {
+        const double a = __shfl_sync(FULLM, ar[jp], gbase + ip);
+        mc[ip] -= a * mc[jp];
+      }
+      double pii = __shfl_sync(FULLM, ar[ip], gbase + ip);
+      fix_pivot(pii);
+      mc[ip] /= pii;
+    }
+    if (on && ok) {
+      for (int s = 0; s < nOwn; ++s)
+#pragma unroll
+        for (int c = 0; c < NV; ++c) ILU[(size_t)(rb + s) * LPB + r * NV + c] = T[s * LPB + r * NV + c];
+      if (d.b.w) __threadfence();
+#pragma unroll
+      for (int m = 0; m < NV; ++m) str(invM + (size_t)i * LPB + m * NV + r, mc[m]);
+    }
+    __syncwarp();
+    ok = __all_sync(FULLM, ok);
+  }
+}
+
 __global__ void k_fill_sentinel_f(size_t n, double* __restrict__ a) {
   const double s = __longlong_as_double((long long)SENTINEL);
   for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (size_t)gridDim.x * blockDim.x) a[i] = s;
@@ -441,6 +680,45 @@ bool factor_symbolic(LinSys& ls) {
     }
     desc.swap(padded);
     ls.factor_slots = (int)desc.size();
+  } else {
+    // k_factor_rows: 32/nVar matrix rows per warp, levels padded to that; usable if every row fits RF_OWN tiles
+    const int rpw = 32 / ls.nVar;
+    bool fits = true;
+    for (const auto& d : desc) fits = fits && (d.a.w - d.a.y <= RF_OWN);
+    ls.factor_rows_ok = fits;
+    if (fits) {
+      std::vector<RowDesc> padded;
+      padded.reserve(desc.size() + (size_t)rpw * ls.lvl_ptr_lower.size());
+      RowDesc empty;
+      empty.a = make_int4(-1, 0, 0, 0);
+      empty.b = make_int4(0, 0, 0, 0);
+      // wide middle (first to last level of at least `wide` rows): k_factor_rows; the narrow head and tail, where the
+      // latency of a level counts and not the rows in it, stay with the warp-per-row kernel
+      static const int wide = getenv("SU2B200_FACTOR_WIDE") ? atoi(getenv("SU2B200_FACTOR_WIDE")) : 4096;
+      int first = -1, last = -1;
+      const int nLev = (int)ls.lvl_ptr_lower.size() - 1;
+      for (int l = 0; l < nLev; ++l)
+        if (ls.lvl_ptr_lower[l + 1] - ls.lvl_ptr_lower[l] >= wide) {
+          if (first < 0) first = l;
+          last = l;
+        }
+      ls.factor_split[0] = ls.factor_split[1] = n;
+      ls.factor_split[2] = ls.factor_split[3] = 0;
+      for (int l = 0; l < nLev; ++l) {
+        if (l == first) {
+          ls.factor_split[0] = ls.lvl_ptr_lower[l];
+          ls.factor_split[2] = (int)(padded.size() / rpw);
+        }
+        for (int t = ls.lvl_ptr_lower[l]; t < ls.lvl_ptr_lower[l + 1]; ++t) padded.push_back(desc[t]);
+        while (padded.size() % rpw) padded.push_back(empty);
+        if (l == last) {
+          ls.factor_split[1] = ls.lvl_ptr_lower[l + 1];
+          ls.factor_split[3] = (int)(padded.size() / rpw);
+        }
+      }
+      ls.factor_groups = (int)(padded.size() / rpw);
+      ls.factor_desc_rows.upload(reinterpret_cast<const int*>(padded.data()), padded.size() * 8);
+    }
   }
   ls.factor_desc.upload(reinterpret_cast<const int*>(desc.data()), desc.size() * 8);
   if (opsLevel.empty()) opsLevel.push_back(make_int2(0, 0));
@@ -452,7 +730,15 @@ bool factor_symbolic(LinSys& ls) {
 }
 
 template <int NV>
-static void factor_launch(su2b200_ctx* c, LinSys& ls) {
+static void fill_invM(su2b200_ctx* c, LinSys& ls) {
+  const size_t nInv = (size_t)ls.Pd * NV * NV;
+  SU2B_LAUNCH(c, k_fill_sentinel_f, (int)std::min<size_t>((nInv + 255) / 256, 148 * 8), 256, nInv, ls.invM.p);
+}
+
+// warp-per-row kernel over the level-ordered rows [begin, end)
+template <int NV>
+static void factor_launch(su2b200_ctx* c, LinSys& ls, int begin, int end) {
+  if (end <= begin) return;
   int dev = 0, nsm = 0, perSm = 0;
   int ownCap = ls.factor_own_cap, srcCap = ls.factor_src_cap;
   const size_t smem = (size_t)4 * 2 * (ownCap + srcCap) * NV * NV * sizeof(double);
@@ -462,11 +748,9 @@ static void factor_launch(su2b200_ctx* c, LinSys& ls) {
   static const int cap = getenv("SU2B200_FACTOR_BLOCKS") ? atoi(getenv("SU2B200_FACTOR_BLOCKS")) : 0;
   if (cap > 0) perSm = std::min(perSm, cap);
   SU2B_REQUIRE(perSm > 0, "ilu factor kernel does not fit an SM");
-  const int grid = std::max(1, std::min((ls.Pd + 3) / 4, nsm * perSm));
-  const size_t nInv = (size_t)ls.Pd * NV * NV;
-  SU2B_LAUNCH(c, k_fill_sentinel_f, (int)std::min<size_t>((nInv + 255) / 256, 148 * 8), 256, nInv, ls.invM.p);
-  int n = ls.Pd;
-  const RowDesc* desc = reinterpret_cast<const RowDesc*>(ls.factor_desc.p);
+  int n = end - begin;
+  const int grid = std::max(1, std::min((n + 3) / 4, nsm * perSm));
+  const RowDesc* desc = reinterpret_cast<const RowDesc*>(ls.factor_desc.p) + begin;
   const int2* ops = reinterpret_cast<const int2*>(ls.factor_ops.p);
   int* ctrl = ls.sweep_ctrl.p;
   const int* ci = ls.col_ind;
@@ -503,12 +787,55 @@ static void factor_launch_scalar(su2b200_ctx* c, LinSys& ls) {
   c->launches++;
 }
 
+// nVar-lanes-per-row kernel over the padded groups [gbeg, gend)
+template <int NV>
+static void factor_launch_rows(su2b200_ctx* c, LinSys& ls, int gbeg, int gend) {
+  if (gend <= gbeg) return;
+  int dev = 0, nsm = 0, perSm = 0;
+  int ownCap = ls.factor_own_cap, srcCap = std::min(ls.factor_src_cap, RF_SRC);
+  const size_t smem = (size_t)4 * (32 / NV) * (ownCap + srcCap + 1) * NV * NV * sizeof(double);
+  SU2B_CUDA(cudaFuncSetAttribute((const void*)k_factor_rows<NV>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                 (int)((size_t)4 * (32 / NV) * (RF_OWN + RF_SRC + 1) * NV * NV * sizeof(double))));
+  SU2B_CUDA(cudaGetDevice(&dev));
+  SU2B_CUDA(cudaDeviceGetAttribute(&nsm, cudaDevAttrMultiProcessorCount, dev));
+  SU2B_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&perSm, k_factor_rows<NV>, 128, smem));
+  static const int capR = getenv("SU2B200_FACTOR_ROWS_BLOCKS") ? atoi(getenv("SU2B200_FACTOR_ROWS_BLOCKS")) : 3;
+  if (capR > 0) perSm = std::min(perSm, capR);
+  SU2B_REQUIRE(perSm > 0, "ilu factor (rows) kernel does not fit an SM");
+  int nGroups = gend - gbeg;
+  const int grid = std::max(1, std::min((nGroups + 3) / 4, nsm * perSm));
+  const RowDesc* desc = reinterpret_cast<const RowDesc*>(ls.factor_desc_rows.p) + (size_t)gbeg * (32 / NV);
+  const int2* ops = reinterpret_cast<const int2*>(ls.factor_ops.p);
+  int* ctrl = ls.sweep_ctrl.p;
+  const int* ci = ls.col_ind;
+  const double* A = ls.A.p;
+  double* ilu = ls.ilu.p;
+  double* invM = ls.invM.p;
+  void* argv[] = {&nGroups, &ownCap, &srcCap, &desc, &ops, &ctrl, &ci, &A, &ilu, &invM};
+  SU2B_CUDA(cudaLaunchCooperativeKernel((const void*)k_factor_rows<NV>, dim3(grid), dim3(128), argv, smem, c->stream));
+  c->launches++;
+}
+
+// block systems: narrow head -> k_factor_poll, wide middle -> k_factor_rows, narrow tail -> k_factor_poll (launches
+// on one stream: a later launch finds everything the earlier ones produced). SU2B200_FACTOR_ROWS=0: one kernel
+// (warp per row) for everything, =2: k_factor_rows for everything.
+template <int NV>
+static void factor_block(su2b200_ctx* c, LinSys& ls) {
+  static const int rows = getenv("SU2B200_FACTOR_ROWS") ? atoi(getenv("SU2B200_FACTOR_ROWS")) : 1;
+  fill_invM<NV>(c, ls);
+  if (rows == 0 || !ls.factor_rows_ok) return factor_launch<NV>(c, ls, 0, ls.Pd);
+  if (rows == 2) return factor_launch_rows<NV>(c, ls, 0, ls.factor_groups);
+  factor_launch<NV>(c, ls, 0, ls.factor_split[0]);
+  factor_launch_rows<NV>(c, ls, ls.factor_split[2], ls.factor_split[3]);
+  factor_launch<NV>(c, ls, ls.factor_split[1], ls.Pd);
+}
+
 // ILU <- factor(A); requires build_levels(ls) and factor_symbolic(ls) == true
 void ilu_factor_poll(su2b200_ctx* c, LinSys& ls) {
   switch (ls.nVar) {
     case 1: factor_launch_scalar(c, ls); break;
-    case 4: factor_launch<4>(c, ls); break;
-    case 5: factor_launch<5>(c, ls); break;
+    case 4: factor_block<4>(c, ls); break;
+    case 5: factor_block<5>(c, ls); break;
     default: throw Error("ilu_factor_poll: unsupported nVar");
   }
 }
