@@ -433,6 +433,15 @@ int su2b200_array_download(su2b200_ctx* c, int which, double* host) {
   SU2B_REQUIRE(host, "null host buffer");
   SU2B_CUDA(cudaStreamSynchronize(c->stream));
   if (n) SU2B_CUDA(cudaMemcpy(host, p, n * sizeof(double), cudaMemcpyDeviceToHost));
+  if (which == SU2B200_ARR_ILU && c->sys[0].ilu_slim) {
+    // slim factors (precond_factor.cu): the upper blocks were never copied out of the Jacobian
+    const LinSys& ls = c->sys[0];
+    const size_t bs = (size_t)ls.nVar * ls.nVar;
+    std::vector<double> a = ls.A.to_host();
+    for (int i = 0; i < ls.Pd; ++i)
+      for (size_t k = (size_t)ls.h_dia_ptr[i] + 1; k < (size_t)ls.h_row_ptr[i + 1]; ++k)
+        std::memcpy(host + k * bs, a.data() + k * bs, bs * sizeof(double));
+  }
   API_END
 }
 int su2b200_array_upload(su2b200_ctx* c, int which, const double* host) {

@@ -149,6 +149,8 @@ struct LinSys {
   bool factor_rows_ok = false;        // every row fits k_factor_rows' tiles
   int factor_groups = 0;              // groups of 32/nVar level-padded rows (k_factor_rows)
   dvec<int> factor_desc_rows;
+  bool upper_stable = false;  // no upper block is ever modified by the factorisation: U_ik == A_ik for k > i
+  bool ilu_slim = false;      // the last build wrote only the lower blocks: the backward sweep reads the upper ones from A
   int factor_split[4] = {0, 0, 0, 0};  // wide middle: level-ordered rows [0],[1]) = padded groups [2],[3])
   int factor_slots = 0;               // scalar systems: level-padded row slots of k_factor_poll_s
   dvec<int> sweep_metar_lower, sweep_metar_upper;  // same, levels padded to 32/nVar rows (k_poll_sweep_rows)

@@ -694,6 +694,7 @@ static void ilu_build_impl(su2b200_ctx* c, LinSys& ls) {
   ls.ilu.alloc(nb);
   ls.invM.alloc((size_t)ls.Pd * NV * NV);
   if (ls.nparts <= 1) build_levels(ls);
+  ls.ilu_slim = false;
   if (ls.nparts <= 1 && ls.build_mode == 2 && factor_symbolic(ls)) {
     ilu_factor_poll(c, ls);  // reads A, writes ILU: no copy
     return;
@@ -730,6 +731,8 @@ static void ilu_apply_impl(su2b200_ctx* c, LinSys& ls, const double* x, double* 
     ilu_apply_poll(c, ls, x, y);
     return;
   }
+  SU2B_REQUIRE(!ls.ilu_slim, "the ILU factors were built for the polling sweeps (upper blocks left in the Jacobian): "
+                             "rebuild the preconditioner after changing the schedule");
   if (x != y) SU2B_CUDA(cudaMemcpyAsync(y, x, n * sizeof(double), cudaMemcpyDeviceToDevice, c->stream));
   if (ls.nparts <= 1 && ls.sweep_mode == 1) {
     int epoch = sweep_begin(c, ls);

@@ -119,7 +119,7 @@ __device__ __forceinline__ double winverse(double a, int r, int c, int q) {
 struct RowDesc { int4 a, b; };
 
 template <int NV>
-__global__ void __launch_bounds__(128, FACTOR_MIN_BLOCKS) k_factor_poll(int n, int ownCap, int srcCap, const RowDesc* __restrict__ desc,
+__global__ void __launch_bounds__(128, FACTOR_MIN_BLOCKS) k_factor_poll(int n, int slim, int ownCap, int srcCap, const RowDesc* __restrict__ desc,
                                                      const int2* __restrict__ ops,
                                                      int* ctrl, const int* __restrict__ col_ind,
                                                      const double* __restrict__ A, double* ILU, double* invM) {
@@ -142,7 +142,7 @@ __global__ void __launch_bounds__(128, FACTOR_MIN_BLOCKS) k_factor_poll(int n, i
     return d.a.y + lane < d.a.z ? col_ind[d.a.y + lane] : 0;
   };
   auto stage = [&](const RowDesc& d, int2 myop, int buf) {
-    const int nOwn = d.a.w - d.a.y;
+    const int nOwn = slim ? d.a.z - d.a.y + 1 : d.a.w - d.a.y;  // slim: the upper blocks are neither changed nor copied
     double* own = sOwn + (size_t)(wib * 2 + buf) * ownCap * LPB;
     double* src = sSrc + (size_t)(wib * 2 + buf) * srcCap * LPB;
     if (act)
@@ -218,8 +218,10 @@ __global__ void __launch_bounds__(128, FACTOR_MIN_BLOCKS) k_factor_poll(int n, i
     }
     const double minv = winverse<NV>(own[nl * LPB + q], r, cc, q);
     if (act) {
-      // every block goes to the ILU matrix (it is not a copy of A any more)
-      for (int s = 0; s < re - rb; ++s) ILU[(size_t)(rb + s) * LPB + q] = own[s * LPB + q];
+      // every block goes to the ILU matrix (it is not a copy of A any more); slim: only the lower ones and the
+      // diagonal, the upper blocks are the Jacobian's own (ls.upper_stable)
+      const int nw = slim ? nl + 1 : re - rb;
+      for (int s = 0; s < nw; ++s) ILU[(size_t)(rb + s) * LPB + q] = own[s * LPB + q];
       if (d0.b.w) __threadfence();
       str(invM + (size_t)i * LPB + q, minv);
     }
@@ -372,7 +374,7 @@ __device__ __forceinline__ bool is_sentinel(double v) {
 }
 
 template <int NV>
-__global__ void __launch_bounds__(128) k_factor_rows(int nGroups, int ownCap, int srcCap, const RowDesc* __restrict__ desc,
+__global__ void __launch_bounds__(128) k_factor_rows(int nGroups, int slim, int ownCap, int srcCap, const RowDesc* __restrict__ desc,
                                                      const int2* __restrict__ ops, int* ctrl,
                                                      const int* __restrict__ col_ind, const double* __restrict__ A,
                                                      double* ILU, double* invM) {
@@ -404,7 +406,7 @@ __global__ void __launch_bounds__(128) k_factor_rows(int nGroups, int ownCap, in
     if (live && g + 2 * W < nGroups) d2 = desc[(size_t)(g + 2 * W) * RPW + sub];
     if (d1.a.x >= 0) {
       const char* nb = reinterpret_cast<const char*>(A + (size_t)d1.a.y * LPB);
-      const int bytes = (d1.a.w - d1.a.y) * LPB * (int)sizeof(double);
+      const int bytes = (slim ? d1.a.z - d1.a.y + 1 : d1.a.w - d1.a.y) * LPB * (int)sizeof(double);
       for (int off = r * 128; off < bytes; off += NV * 128) asm volatile("prefetch.global.L2 [%0];" ::"l"(nb + off));
       if (r == 0) asm volatile("prefetch.global.L2 [%0];" ::"l"(col_ind + d1.a.y));
       if (r == 1 && d1.b.y > 0) asm volatile("prefetch.global.L2 [%0];" ::"l"(ops + d1.b.x));
@@ -415,7 +417,8 @@ __global__ void __launch_bounds__(128) k_factor_rows(int nGroups, int ownCap, in
     // the row itself (asynchronous copies into its tiles), the first update ops and the columns of the lower entries
     // in one round of loads, then the first look at the awaited inverse diagonals (row r of each) and the staged
     // sources: three dependent rounds of memory latency per group instead of one per array
-    for (int s = 0; s < nOwn; ++s)
+    const int nLoad = slim ? min(nl + 1, nOwn) : nOwn;  // slim: the upper blocks are neither changed nor copied
+    for (int s = 0; s < nLoad; ++s)
 #pragma unroll
       for (int c = 0; c < NV; ++c) cp_async8(T + s * LPB + r * NV + c, A + (size_t)(rb + s) * LPB + r * NV + c);
     int2 opr[RF_SRC];
@@ -582,7 +585,8 @@ __global__ void __launch_bounds__(128) k_factor_rows(int nGroups, int ownCap, in
       mc[ip] /= pii;
     }
     if (on && ok) {
-      for (int s = 0; s < nOwn; ++s)
+      const int nw = slim ? nLoad : nOwn;
+      for (int s = 0; s < nw; ++s)
 #pragma unroll
         for (int c = 0; c < NV; ++c) ILU[(size_t)(rb + s) * LPB + r * NV + c] = T[s * LPB + r * NV + c];
       if (d.b.w) __threadfence();
@@ -637,6 +641,10 @@ bool factor_symbolic(LinSys& ls) {
   // pass 2: stable sources, write-back masks, fence flags; descriptors in level order
   for (auto& op : opList)
     if (!modified[op.x]) op.x = (int)((unsigned)op.x | STABLE);
+  ls.upper_stable = true;
+  for (int i = 0; i < n && ls.upper_stable; ++i)
+    for (int s = dp[i] + 1; s < rp[i + 1]; ++s)
+      if (modified[s]) { ls.upper_stable = false; break; }
   const std::vector<int> rows = ls.lvl_rows_lower.to_host();
   std::vector<RowDesc> desc(n);
   int maxOwn = 1, maxOps = 0;
@@ -757,7 +765,8 @@ static void factor_launch(su2b200_ctx* c, LinSys& ls, int begin, int end) {
   const double* A = ls.A.p;
   double* ilu = ls.ilu.p;
   double* invM = ls.invM.p;
-  void* argv[] = {&n, &ownCap, &srcCap, &desc, &ops, &ctrl, &ci, &A, &ilu, &invM};
+  int slim = ls.ilu_slim ? 1 : 0;
+  void* argv[] = {&n, &slim, &ownCap, &srcCap, &desc, &ops, &ctrl, &ci, &A, &ilu, &invM};
   SU2B_CUDA(cudaLaunchCooperativeKernel((const void*)k_factor_poll<NV>, dim3(grid), dim3(128), argv, smem, c->stream));
   c->launches++;
 }
@@ -811,7 +820,8 @@ static void factor_launch_rows(su2b200_ctx* c, LinSys& ls, int gbeg, int gend) {
   const double* A = ls.A.p;
   double* ilu = ls.ilu.p;
   double* invM = ls.invM.p;
-  void* argv[] = {&nGroups, &ownCap, &srcCap, &desc, &ops, &ctrl, &ci, &A, &ilu, &invM};
+  int slim = ls.ilu_slim ? 1 : 0;
+  void* argv[] = {&nGroups, &slim, &ownCap, &srcCap, &desc, &ops, &ctrl, &ci, &A, &ilu, &invM};
   SU2B_CUDA(cudaLaunchCooperativeKernel((const void*)k_factor_rows<NV>, dim3(grid), dim3(128), argv, smem, c->stream));
   c->launches++;
 }
@@ -822,6 +832,10 @@ static void factor_launch_rows(su2b200_ctx* c, LinSys& ls, int gbeg, int gend) {
 template <int NV>
 static void factor_block(su2b200_ctx* c, LinSys& ls) {
   static const int rows = getenv("SU2B200_FACTOR_ROWS") ? atoi(getenv("SU2B200_FACTOR_ROWS")) : 1;
+  // slim ILU: when no upper block changes (7-point hexahedral stencils: every update lands on a diagonal) and the
+  // polling sweeps are the consumer, the upper blocks stay in the Jacobian: not read, not written here
+  static const int slimOk = getenv("SU2B200_ILU_SLIM") ? atoi(getenv("SU2B200_ILU_SLIM")) : 1;
+  ls.ilu_slim = slimOk && ls.upper_stable && ls.sweep_mode == 2;
   fill_invM<NV>(c, ls);
   if (rows == 0 || !ls.factor_rows_ok) return factor_launch<NV>(c, ls, 0, ls.Pd);
   if (rows == 2) return factor_launch_rows<NV>(c, ls, 0, ls.factor_groups);

@@ -556,6 +556,8 @@ static void ilu_apply_poll_impl(su2b200_ctx* c, LinSys& ls, const double* x, dou
   const int4* mu = reinterpret_cast<const int4*>(ls.sweep_meta_upper.p);
   const int* ci = ls.col_ind;
   const double* ilu = ls.ilu.p;
+  // slim ILU (precond_factor.cu): the factorisation left the upper blocks where they were, in the Jacobian
+  const double* iluU = (NV > 1 && ls.ilu_slim) ? ls.A.p : ls.ilu.p;
   const double* invM = ls.invM.p;
   int* ctrl = ls.sweep_ctrl.p;
   // resident blocks per SM: every waiting lane of a scalar sweep polls its own sector, so too many waiting warps
@@ -575,7 +577,7 @@ static void ilu_apply_poll_impl(su2b200_ctx* c, LinSys& ls, const double* x, dou
       // per row) -> k_poll_sweep_rows. Up to three launches per sweep, split at level boundaries.
       const int4* mrl = reinterpret_cast<const int4*>(ls.sweep_metar_lower.p);
       const int4* mru = reinterpret_cast<const int4*>(ls.sweep_metar_upper.p);
-      auto sweep = [&](auto narrowK, auto wideK, const int4* mnar, const int4* mwid, const int (&sp)[4], int nGroups,
+      auto sweep = [&](auto narrowK, auto wideK, const int4* mnar, const int4* mwid, const int (&sp)[4], const double* ilu,
                        const double* src, double* dst) {
         const int nRows = ls.Pd;
         if (sp[0] > 0) launch_resident(c, narrowK, (sp[0] + 3) / 4, capB, sp[0], mnar, ctrl, ci, ilu, invM, src, dst);
@@ -584,19 +586,17 @@ static void ilu_apply_poll_impl(su2b200_ctx* c, LinSys& ls, const double* x, dou
                           ilu, invM, src, dst);
         if (nRows > sp[2])
           launch_resident(c, narrowK, (nRows - sp[2] + 3) / 4, capB, nRows - sp[2], mnar + sp[2], ctrl, ci, ilu, invM, src, dst);
-        (void)nGroups;
       };
-      sweep(k_poll_sweep<NV, true>, k_poll_sweep_rows<NV, true>, ml, mrl, ls.poll_split_lower, ls.poll_groups_lower, x, w);
-      sweep(k_poll_sweep<NV, false>, k_poll_sweep_rows<NV, false>, mu, mru, ls.poll_split_upper, ls.poll_groups_upper,
-            (const double*)w, y);
+      sweep(k_poll_sweep<NV, true>, k_poll_sweep_rows<NV, true>, ml, mrl, ls.poll_split_lower, ilu, x, w);
+      sweep(k_poll_sweep<NV, false>, k_poll_sweep_rows<NV, false>, mu, mru, ls.poll_split_upper, iluU, (const double*)w, y);
     } else if (pipe) {
       const size_t smem = (size_t)4 * PIPE * sizeof(SweepStage<NV>);
       launch_resident_smem(c, k_poll_sweep_pipe<NV, true>, smem, (ls.Pd + 3) / 4, capB, ls.Pd, ml, ctrl, ci, ilu, invM, x, w);
-      launch_resident_smem(c, k_poll_sweep_pipe<NV, false>, smem, (ls.Pd + 3) / 4, capB, ls.Pd, mu, ctrl, ci, ilu, invM,
+      launch_resident_smem(c, k_poll_sweep_pipe<NV, false>, smem, (ls.Pd + 3) / 4, capB, ls.Pd, mu, ctrl, ci, iluU, invM,
                            (const double*)w, y);
     } else {
       launch_resident(c, k_poll_sweep<NV, true>, (ls.Pd + 3) / 4, capB, ls.Pd, ml, ctrl, ci, ilu, invM, x, w);
-      launch_resident(c, k_poll_sweep<NV, false>, (ls.Pd + 3) / 4, capB, ls.Pd, mu, ctrl, ci, ilu, invM, (const double*)w, y);
+      launch_resident(c, k_poll_sweep<NV, false>, (ls.Pd + 3) / 4, capB, ls.Pd, mu, ctrl, ci, iluU, invM, (const double*)w, y);
     }
   }
 }
