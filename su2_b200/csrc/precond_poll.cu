@@ -598,9 +598,8 @@ static void ilu_apply_poll_impl(su2b200_ctx* c, LinSys& ls, const double* x, dou
   const double* iluU = (NV > 1 && ls.ilu_slim) ? ls.A.p : ls.ilu.p;
   const double* invM = ls.invM.p;
   int* ctrl = ls.sweep_ctrl.p;
-  // resident blocks per SM: every waiting lane of a scalar sweep polls its own sector, so too many waiting warps
-  // saturate L2 with polls and slow the rows on the critical path; block rows poll one or two sectors per warp
-  static const int capS = getenv("SU2B200_SWEEP_BLOCKS_S") ? atoi(getenv("SU2B200_SWEEP_BLOCKS_S")) : 4;
+  // resident blocks per SM (0 = what fits): with warp-converged polling more resident warps only help
+  static const int capS = getenv("SU2B200_SWEEP_BLOCKS_S") ? atoi(getenv("SU2B200_SWEEP_BLOCKS_S")) : 0;
   static const int capB = getenv("SU2B200_SWEEP_BLOCKS") ? atoi(getenv("SU2B200_SWEEP_BLOCKS")) : 0;
   if constexpr (NV == 1) {
     launch_resident(c, k_poll_sweep_s<true>, (ls.poll_groups_lower + 3) / 4, capS, ls.poll_groups_lower, ml, ctrl, ci, ilu, invM, x, w);
