@@ -172,6 +172,7 @@ int su2b200_geometry_upload(su2b200_ctx* c, const su2b200_geometry_desc* d) {
   std::vector<int> nn(P);
   for (int i = 0; i < P; ++i) nn[i] = d->nNeighbor ? (int)d->nNeighbor[i] : nptr[i + 1] - nptr[i];
   g.nnbr.upload(nn);
+  g.nnbr_global = false;
   std::vector<unsigned char> pb(P, 0);
   if (d->physical_boundary) pb.assign(d->physical_boundary, d->physical_boundary + P);
   g.phys_bnd.upload(pb);
@@ -322,6 +323,21 @@ int su2b200_flow_allocate(su2b200_ctx* c) {
   s.nG = nd + 2;
   const int nv = s.nVar;
   auto alloc0 = [](dvec<double>& v, size_t n) { v.alloc(n); v.zero(); };
+  if (c->nranks > 1 && !g.nnbr_global) {
+    // CPoint::nNeighbor of a halo point is the count on its owner (the local neighbour list of a halo point is
+    // incomplete); the JST coefficients of an edge use it for both end points (centered.hpp:123-127)
+    std::vector<int> nn = g.nnbr.to_host();
+    std::vector<double> t(nn.begin(), nn.end());
+    dvec<double> d;
+    d.upload(t);
+    SU2B_CUDA(cudaDeviceSynchronize());
+    halo_exchange(c, d.p, 1);
+    SU2B_CUDA(cudaDeviceSynchronize());
+    t = d.to_host();
+    for (size_t i = 0; i < nn.size(); ++i) nn[i] = (int)(t[i] + 0.5);
+    g.nnbr.upload(nn);
+    g.nnbr_global = true;
+  }
   alloc0(s.U, (size_t)P * nv);
   alloc0(s.U_old, (size_t)P * nv);
   alloc0(s.V, (size_t)P * s.nPrim);

@@ -103,6 +103,7 @@ struct Geometry {
   dvec<int> edge_ij, edge_ji;     // [E] block index of (i,j) and (j,i)
   dvec<int> gat_edge, gat_blk;    // per-point edge list sorted by edge index (see k_point_sum)
   dvec<int> nnbr;                 // CPoint::nNeighbor
+  bool nnbr_global = false;       // halo entries of nnbr hold the owner's count (set once comm is up)
   dvec<unsigned char> phys_bnd;   // CPoint::PhysicalBoundary
   dvec<double> wall_dist;
   // edge colouring (COLORED assembly)

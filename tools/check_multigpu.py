@@ -1,6 +1,6 @@
 """Multi-GPU parity of the first implicit iteration: N slabs over NCCL against the undivided mesh on one GPU.
 
-torchrun --nproc-per-node N tools/check_multigpu.py [EULER|NAVIER_STOKES|RANS]
+torchrun --nproc-per-node N tools/check_multigpu.py [EULER|NAVIER_STOKES|RANS|EULER_JST|NAVIER_STOKES_JST]
 Every rank assembles the residual of iteration 0 on its slab (halo exchange of solution, gradients, limiters, nu~);
 rank 0 also runs the undivided mesh and compares, by global point index, the rhs vector, the local time steps, the
 limiters and the rms residuals: they must agree to round-off (the preconditioner is the only rank-dependent part of an
@@ -46,7 +46,13 @@ def first_iteration(opts, rank, world, device, comm=None):
     rms, _, _ = s.PrepareImplicitIteration()
     out["rhs"] = s.get("LINSYSRES").reshape(-1, nv)[:Pd]
     out["dt"] = s.get("DELTA_TIME")[:Pd]
-    out["lim"] = s.get("LIMITER").reshape(len(gid), -1)[:Pd]
+    lim = s.get("LIMITER")
+    if lim.size:
+        out["lim"] = lim.reshape(len(gid), -1)[:Pd]
+    for name, key in (("SENSOR", "sensor"), ("UND_LAPL", "lapl"), ("LAMBDA", "lambda")):
+        a = s.get(name)
+        if a.size:
+            out[key] = a.reshape(len(gid), -1)[:Pd]
     out["rms"] = rms
     if rans:
         s.Turb_Preprocessing()
@@ -65,7 +71,11 @@ def main():
     torch.cuda.set_device(local)
     dist.init_process_group("nccl", device_id=torch.device("cuda", local))
     n = [12, 10, 8 * world + 1]
-    opts = parse_cfg(bench.make_cfg(kind, n, 1))
+    jst = kind.endswith("_JST")
+    text = bench.make_cfg(kind[:-4] if jst else kind, n, 1)
+    if jst:  # centred scheme: max eigenvalue, pressure sensor and undivided Laplacian are exchanged as well
+        text = text.replace("CONV_NUM_METHOD_FLOW= ROE", "CONV_NUM_METHOD_FLOW= JST").replace("MUSCL_FLOW= YES", "MUSCL_FLOW= NO")
+    opts = parse_cfg(text)
 
     def comm(s):
         idbuf = torch.zeros(128, dtype=torch.uint8, device="cuda")
@@ -84,7 +94,7 @@ def main():
         pos = {int(g): k for k, g in enumerate(gw)}
         for g, part in parts:
             idx = np.array([pos[int(x)] for x in g])
-            for key in ("rhs", "dt", "lim", "turb_rhs"):
+            for key in ("rhs", "dt", "lim", "sensor", "lapl", "lambda", "turb_rhs"):
                 if key not in part:
                     continue
                 a, b = part[key], whole[key][idx]
