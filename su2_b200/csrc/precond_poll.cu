@@ -350,30 +350,31 @@ __global__ void __launch_bounds__(128, ROWS_MIN_BLOCKS) k_poll_sweep_rows(int nG
 #pragma unroll
       for (int c = 0; c < NV; ++c) dinv[c] = on ? invM[(size_t)i * LPB + r * NV + c] : 0.0;
     }
-    // first look at every dependency, then wait only for what is missing
-    double y[CH][NV];
+    // lane r watches component r of every dependency (one or two sectors per row and dependency: with each lane
+    // re-reading all nVar components the waiting warps saturated the L2 and the hop from level to level took 2.4 us);
+    // first look at all of them, then all that is still missing again per round, the warp as one instruction stream
+    double mine[CH];
 #pragma unroll
-    for (int k = 0; k < CH; ++k)
-#pragma unroll
-      for (int c = 0; c < NV; ++c)
-        y[k][c] = (on && kb + k < ke) ? ld_relaxed(out + (size_t)jj[k] * NV + c) : 0.0;
-    // whatever is still missing is looked at again, all of it per round (one L2 round trip per round, not per value)
+    for (int k = 0; k < CH; ++k) mine[k] = (on && kb + k < ke) ? ld_relaxed(out + (size_t)jj[k] * NV + r) : 0.0;
     for (unsigned spins = 0;; ++spins) {
       bool miss = false;
 #pragma unroll
       for (int k = 0; k < CH; ++k)
-#pragma unroll
-        for (int c = 0; c < NV; ++c)
-          if ((unsigned long long)__double_as_longlong(y[k][c]) == SENTINEL) {
-            miss = true;
-            y[k][c] = ld_relaxed(out + (size_t)jj[k] * NV + c);
-          }
-      if (!miss) break;
+        if ((unsigned long long)__double_as_longlong(mine[k]) == SENTINEL) {
+          miss = true;
+          mine[k] = ld_relaxed(out + (size_t)jj[k] * NV + r);
+        }
+      if (!__any_sync(FULLM, miss)) break;
       if ((spins & 1023u) == 1023u) {
         if (spins > (1u << 22)) atomicExch(ctrl + 1, 1);
-        if (ld_relaxed_i(ctrl + 1) != 0) { ok = false; break; }
+        if (__any_sync(FULLM, ld_relaxed_i(ctrl + 1) != 0)) { ok = false; break; }
       }
     }
+    double y[CH][NV];
+#pragma unroll
+    for (int k = 0; k < CH; ++k)
+#pragma unroll
+      for (int c = 0; c < NV; ++c) y[k][c] = __shfl_sync(FULLM, mine[k], sub * NV + c);
 #pragma unroll
     for (int k = 0; k < CH; ++k) {
       if (on && ok && kb + k < ke) {
@@ -564,7 +565,7 @@ static void build_meta(LinSys& ls) {
     // hybrid schedule: the contiguous run of wide levels [first, last] goes to the rows kernel, the narrow head and tail
     // to the warp-per-row kernel. split = {rows before the run, groups before the run, rows at its end, groups at its end}
     // (185^3, ms per application: threshold 1024 -> 3.75, 4096 -> 3.53, 16384 -> 3.46; warp-per-row only 3.97)
-    const int wide = getenv("SU2B200_SWEEP_WIDE") ? atoi(getenv("SU2B200_SWEEP_WIDE")) : 16384;
+    const int wide = getenv("SU2B200_SWEEP_WIDE") ? atoi(getenv("SU2B200_SWEEP_WIDE")) : 4096;
     auto split = [&](const std::vector<int>& ptr, int (&sp)[4]) {
       const int nl = (int)ptr.size() - 1;
       int first = -1, last = -1;
