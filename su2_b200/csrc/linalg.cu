@@ -189,6 +189,54 @@ __global__ void __launch_bounds__(256) k_spmv(int Pd, const int* __restrict__ ro
   if (active && g == 0 && cc == 0) y[(size_t)warp * NV + q / NV] = s;
 }
 
+// nVar lanes per block row, 32/nVar rows per warp: lane r owns component r of its row's product and walks the row's
+// blocks in the reference's order (RowProduct, CSysMatrix.inl:173-181: blocks outer, columns inner, one accumulation
+// chain per component). A warp reads the blocks of 6
+// consecutive rows = one contiguous 8 KB stretch of the matrix; nothing is reduced across lanes. This is the mapping
+// that took the wide levels of the ILU sweeps to 85 % of the HBM peak (precond_poll.cu: k_poll_sweep_rows).
+// Measured on 185^3 (ms): blocks per step / resident blocks per SM = 7/2 2.02, 4/4 1.83, 3/5 1.77, 2/6 1.58, 1/8 1.52,
+// 1/12 1.49 — occupancy beats loads in flight per lane; the old warp-per-row kernel: 2.31.
+#ifndef SPMV_ROWS_CH
+#define SPMV_ROWS_CH 1
+#endif
+#ifndef SPMV_ROWS_MIN_BLOCKS
+#define SPMV_ROWS_MIN_BLOCKS 12
+#endif
+template <int NV>
+__global__ void __launch_bounds__(128, SPMV_ROWS_MIN_BLOCKS) k_spmv_rows(int Pd, const int* __restrict__ row_ptr,
+                                                                         const int* __restrict__ col_ind,
+                                                                         const double* __restrict__ A,
+                                                                         const double* __restrict__ x, double* __restrict__ y) {
+  constexpr int LPB = NV * NV, RPW = 32 / NV, CH = SPMV_ROWS_CH;
+  const int lane = threadIdx.x & 31, sub = lane / NV, r = lane % NV;
+  const long wg = ((long)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+  const long row = wg * RPW + sub;
+  const bool on = sub < RPW && row < Pd;
+  const int kb = on ? row_ptr[row] : 0, ke = on ? row_ptr[row + 1] : 0;
+  double acc = 0.0;
+  for (int k0 = kb; k0 < ke; k0 += CH) {
+    int col[CH];
+    double a[CH][NV], xv[CH][NV];
+#pragma unroll
+    for (int u = 0; u < CH; ++u) col[u] = k0 + u < ke ? col_ind[k0 + u] : 0;
+#pragma unroll
+    for (int u = 0; u < CH; ++u)
+#pragma unroll
+      for (int c = 0; c < NV; ++c) a[u][c] = k0 + u < ke ? A[(size_t)(k0 + u) * LPB + r * NV + c] : 0.0;
+#pragma unroll
+    for (int u = 0; u < CH; ++u)
+#pragma unroll
+      for (int c = 0; c < NV; ++c) xv[u][c] = k0 + u < ke ? x[(size_t)col[u] * NV + c] : 0.0;
+#pragma unroll
+    for (int u = 0; u < CH; ++u)
+      if (k0 + u < ke) {
+#pragma unroll
+        for (int c = 0; c < NV; ++c) acc += a[u][c] * xv[u][c];
+      }
+  }
+  if (on) y[(size_t)row * NV + r] = acc;
+}
+
 // scalar CSR (nVar == 1): 8 lanes per row
 __global__ void __launch_bounds__(256) k_spmv_scalar(int Pd, const int* __restrict__ row_ptr,
                                                      const int* __restrict__ col_ind, const double* __restrict__ A,
@@ -208,6 +256,15 @@ __global__ void __launch_bounds__(256) k_spmv_scalar(int Pd, const int* __restri
 void linsys_spmv(su2b200_ctx* c, LinSys& ls, const double* x, double* y) {
   ProfScope prof_(c, PROF_SPMV);
   const long threads = (long)ls.Pd * 32;
+  static const int rowsK = getenv("SU2B200_SPMV_ROWS") ? atoi(getenv("SU2B200_SPMV_ROWS")) : 1;
+  if (rowsK && ls.nVar > 1) {
+    const long warps = ((long)ls.Pd + 32 / ls.nVar - 1) / (32 / ls.nVar);
+    if (ls.nVar == 4) SU2B_LAUNCH(c, k_spmv_rows<4>, nblk(warps * 32, 128), 128, ls.Pd, ls.row_ptr, ls.col_ind, ls.A.p, x, y);
+    else if (ls.nVar == 5) SU2B_LAUNCH(c, k_spmv_rows<5>, nblk(warps * 32, 128), 128, ls.Pd, ls.row_ptr, ls.col_ind, ls.A.p, x, y);
+    else throw Error("linsys_spmv: unsupported nVar");
+    if (c->nranks > 1) halo_exchange(c, y, ls.nVar);
+    return;
+  }
   switch (ls.nVar) {
     case 1: SU2B_LAUNCH(c, k_spmv_scalar, nblk((long)ls.Pd * 8, 256), 256, ls.Pd, ls.row_ptr, ls.col_ind, ls.A.p, x, y); break;
     case 4: SU2B_LAUNCH(c, k_spmv<4>, nblk(threads, 256), 256, ls.Pd, ls.row_ptr, ls.col_ind, ls.A.p, x, y); break;
