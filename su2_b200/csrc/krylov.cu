@@ -83,12 +83,30 @@ __global__ void __launch_bounds__(256) k_mgs_dot(size_t n_owned, size_t n_all, d
                                                   double* __restrict__ part) {
   if (need_flag && sc[3] == 0.0) return;
   const double coef = vprev ? sc[0] : 0.0;
-  double s = 0.0;
-  for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < n_all; i += (size_t)gridDim.x * blockDim.x) {
+  // four independent element streams per thread (loads of a round issued together), fixed summation order
+  const size_t stride = (size_t)gridDim.x * blockDim.x;
+  size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+  double acc[4] = {0.0, 0.0, 0.0, 0.0};
+  for (; i + 3 * stride < n_all; i += 4 * stride) {
+    double wi[4], pv[4], kv[4];
+#pragma unroll
+    for (int u = 0; u < 4; ++u) wi[u] = w[i + u * stride];
+#pragma unroll
+    for (int u = 0; u < 4; ++u) pv[u] = vprev ? vprev[i + u * stride] : 0.0;
+#pragma unroll
+    for (int u = 0; u < 4; ++u) kv[u] = vk ? vk[i + u * stride] : 0.0;
+#pragma unroll
+    for (int u = 0; u < 4; ++u) {
+      if (vprev) { wi[u] += -coef * pv[u]; w[i + u * stride] = wi[u]; }
+      if (i + u * stride < n_owned) acc[u] += wi[u] * (vk ? kv[u] : wi[u]);
+    }
+  }
+  for (; i < n_all; i += stride) {
     double wi = w[i];
     if (vprev) { wi += -coef * vprev[i]; w[i] = wi; }
-    if (i < n_owned) s += wi * (vk ? vk[i] : wi);
+    if (i < n_owned) acc[0] += wi * (vk ? vk[i] : wi);
   }
+  double s = (acc[0] + acc[1]) + (acc[2] + acc[3]);
   __shared__ double sm[32];
   for (int o = 16; o > 0; o >>= 1) s += __shfl_xor_sync(0xffffffffu, s, o);
   const int wp = threadIdx.x >> 5, l = threadIdx.x & 31;
