@@ -289,11 +289,14 @@ __device__ __forceinline__ void scalar_dissipation_jacobian(const double* V, dou
 // LEGACY = the boundary functor CAvgGrad_Flow (flow_diffusion.cpp:368-532): same flux, but its heat-flux Jacobian
 // uses cp/R * (k/cp + mu_t/Pr_t) (SetHeatFluxJacobian :489-532), which differs from the SIMD form when the mean cp
 // is not the gas cp (far-field state carries cp = k = 0, CEulerSolver.cpp:4990-4993).
-template <int ND, bool IMPLICIT, bool LEGACY = false, class JT = double*>
+// `gmean` (optional): the mean gradient 0.5*gi + 0.5*gj already formed by the caller (the staged edge kernel keeps it
+// in shared memory); used instead of gi/gj when `have_mean`.
+template <int ND, bool IMPLICIT, bool LEGACY = false, class JT = double*, class GM = const double*>
 __device__ __forceinline__ void viscous_terms(const FlowParams& p, const double* Vi, const double* Vj,
                                               const double* gi, const double* gj, const double* vec_ij,
                                               double area, const double* un, bool correct,
-                                              double* flux, JT jac_i, JT jac_j) {
+                                              double* flux, JT jac_i, JT jac_j, bool have_mean = false,
+                                              GM gmean = GM()) {
   using I = PrimIdx<ND>;
   constexpr int NV = ND + 2;
   constexpr int NG = ND + 1;
@@ -309,10 +312,14 @@ __device__ __forceinline__ void viscous_terms(const FlowParams& p, const double*
   double g[NG * ND];
 #pragma unroll
   for (int k = 0; k < NG * ND; ++k) {
-    double a = gi[k];
-    a *= 0.5;
-    a += 0.5 * gj[k];
-    g[k] = a;
+    if (have_mean) {
+      g[k] = gmean[k];
+    } else {
+      double a = gi[k];
+      a *= 0.5;
+      a += 0.5 * gj[k];
+      g[k] = a;
+    }
   }
   if (correct) {
 #pragma unroll

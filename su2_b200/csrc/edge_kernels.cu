@@ -50,7 +50,9 @@ struct EdgeArgs {
 // --- MUSCL reconstruction: reconstructPrimitives (common.hpp:194-279) with musclPointLimited (:113-141) /
 //     musclUnlimited (:84-108). Returns true if the edge falls back to first order.
 template <int ND>
-__device__ __forceinline__ void muscl_reconstruct(const FlowParams& p, const EdgeArgs& a, int e, int i, int j,
+__device__ __forceinline__ void muscl_reconstruct(const FlowParams& p, const EdgeArgs& a, int e,
+                                                  const double* gi, const double* gj,  // reconstruction gradients
+                                                  const double* lim_i, const double* lim_j,  // point limiters
                                                   const double* Vi1, const double* Vj1, const double* vij,
                                                   double* Vi, double* Vj) {
   using I = PrimIdx<ND>;
@@ -58,8 +60,6 @@ __device__ __forceinline__ void muscl_reconstruct(const FlowParams& p, const Edg
   constexpr int NGR = ND + 2;  // variables with gradients (T, v, P)
 #pragma unroll
   for (int k = 0; k < NR; ++k) { Vi[k] = Vi1[k]; Vj[k] = Vj1[k]; }
-  const double* gi = a.grad_rec + (size_t)i * a.ngs * ND;
-  const double* gj = a.grad_rec + (size_t)j * a.ngs * ND;
 #pragma unroll
   for (int v = 0; v < NGR; ++v) {
     const double delta = Vj[v] - Vi[v];
@@ -70,8 +70,8 @@ __device__ __forceinline__ void muscl_reconstruct(const FlowParams& p, const Edg
     const double proj_i = 1.0 * ((1.0 - p.muscl_kappa) * pi_ + p.muscl_kappa * delta);
     const double proj_j = 1.0 * ((1.0 - p.muscl_kappa) * pj_ + p.muscl_kappa * delta);
     if (p.limiter) {
-      const double li = a.limiter[(size_t)i * NGR + v];
-      const double lj = a.limiter[(size_t)j * NGR + v];
+      const double li = lim_i[v];
+      const double lj = lim_j[v];
       Vi[v] += 0.5 * li * proj_i;
       Vj[v] -= 0.5 * lj * proj_j;
     } else {
@@ -111,14 +111,11 @@ __device__ __forceinline__ void muscl_reconstruct(const FlowParams& p, const Edg
 }
 
 // The two Jacobian blocks of an edge live in shared memory while the thread builds them (entry k of thread t at
-// [k * JSTRIDE + t]: conflict-free for the owning thread, and for the 25 lanes that later read one edge's block),
+// [k * JSTRIDE + lane] of the warp's tile: conflict-free for the owning thread, and for the 25 lanes that later read one
+// edge's block),
 // which takes 100 registers off the thread and lets the warp write every 200-byte block as one contiguous store.
 #ifndef EDGE_MIN_BLOCKS
 #define EDGE_MIN_BLOCKS 3  // resident blocks per SM the register allocation aims at
-#endif
-#ifndef EDGE_PER_THREAD
-#define EDGE_PER_THREAD 1  // edges a thread of the Roe kernel processes in sequence, next edge's data prefetched
-                           // (measured on 129^3: 1 -> 1.919 ms, 2 -> 1.916 ms, 4 -> 3.26 ms: no gain, kept at 1)
 #endif
 static constexpr int EDGE_BLOCK = 128;
 // per-edge data is touched once per sweep (indices, normals, flux, Jacobian blocks): streaming loads / stores keep the
@@ -132,24 +129,23 @@ static constexpr int EDGE_BLOCK = 128;
 #define ST_ONCE(p, v) __stcs((p), (v))
 #endif
 
-__device__ __forceinline__ void prefetch_lines(const void* first, size_t bytes) {
-  const char* p = static_cast<const char*>(first);
-  asm volatile("prefetch.global.L1 [%0];" ::"l"(p));
-  asm volatile("prefetch.global.L1 [%0];" ::"l"(p + bytes - 1));  // a record may straddle two 128-byte lines
-}
-static constexpr int JSTRIDE = EDGE_BLOCK + 1;
+// warp-major tiles: warp w owns sjac[w * rows * JSTRIDE ...], entry k of its lane l at [k * JSTRIDE + l]
+static constexpr int JSTRIDE = 33;
 struct SmemJac {
   double* p;
   __device__ __forceinline__ double& operator[](int k) const { return p[k * JSTRIDE]; }
 };
 template <int NV>
-static constexpr size_t edge_smem_bytes() { return (size_t)2 * NV * NV * JSTRIDE * sizeof(double); }
+static constexpr size_t edge_smem_bytes(int extra_rows = 0) {
+  return (size_t)(EDGE_BLOCK / 32) * (2 * NV * NV + extra_rows) * JSTRIDE * sizeof(double);
+}
 
 // flux (GATHER) or residual/diagonal read-modify-write (COLORED) by the owning thread, then the off-diagonal blocks
 // J_ij = jac_j, J_ji = -jac_i by the whole warp: for each of its 32 edges, lanes 0..NV*NV-1 store one block.
 template <int ND, bool COLORED>
 __device__ __forceinline__ void store_edge_outputs(const EdgeArgs& a, bool valid, int e, int i, int j, int bij, int bji,
-                                                   const double* flux, SmemJac jac_i, SmemJac jac_j, double* sjac) {
+                                                   const double* flux, SmemJac jac_i, SmemJac jac_j,
+                                                   const double* wtile) {
   constexpr int NV = ND + 2;
   if (valid) {
     if (!COLORED) {
@@ -165,9 +161,9 @@ __device__ __forceinline__ void store_edge_outputs(const EdgeArgs& a, bool valid
     }
   }
   __syncwarp();
-  const int lane = threadIdx.x & 31, wbase = threadIdx.x & ~31;
-  const double* si = sjac + wbase;
-  const double* sj = sjac + NV * NV * JSTRIDE + wbase;
+  const int lane = threadIdx.x & 31;
+  const double* si = wtile;
+  const double* sj = wtile + NV * NV * JSTRIDE;
 #pragma unroll 4
   for (int t = 0; t < 32; ++t) {
     const int dst_ij = __shfl_sync(0xffffffffu, bij, t);
@@ -181,89 +177,185 @@ __device__ __forceinline__ void store_edge_outputs(const EdgeArgs& a, bool valid
   }
 }
 
-// pull the records of point x that an edge gathers (state, reconstruction gradient, limiter, viscous gradient, coords)
-template <int ND, bool VISC>
-__device__ __forceinline__ void prefetch_point(const EdgeArgs& a, int x) {
-  using I = PrimIdx<ND>;
-  prefetch_lines(a.V + (size_t)x * I::NPRIM, (VISC ? ND + 9 : ND + 4) * sizeof(double));
-  prefetch_lines(a.grad_rec + (size_t)x * a.ngs * ND, (size_t)(ND + 2) * ND * sizeof(double));
-  prefetch_lines(a.limiter + (size_t)x * (ND + 2), (ND + 2) * sizeof(double));
-  if (VISC && a.grad_prim != a.grad_rec)
-    prefetch_lines(a.grad_prim + (size_t)x * a.ngs * ND, (size_t)(ND + 1) * ND * sizeof(double));
-  prefetch_lines(a.coord + (size_t)x * ND, ND * sizeof(double));
+// ------------------------------------------------------------------------------------------------
+// Staged gathers (experiment). A thread that reads its own point records (AoS, 24..120 bytes each) with scalar loads
+// makes every load instruction touch up to 32 different 128-byte lines, and the L1 data pipe is the busiest unit of the
+// kernel (75 %). Here the WARP loads the 32 records of its 32 edges with consecutive lanes on consecutive doubles (1-2 lines per
+// record), and the records are handed to their owning lanes through shared memory. The scratch is the warp's slice of
+// the Jacobian tile, which is not in use before the flux is computed.
+// ------------------------------------------------------------------------------------------------
+// MEASURED AND NOT ADOPTED (185^3 RANS, B200): 5.46 ms staged against 4.80 ms with the direct gathers below. ncu on 129^3
+// (profiles/r01_ncu_edge_staging.txt): L1 sectors of the global loads 401 M -> 110 M and the data-pipe wavefronts per SM
+// 2.57 M -> 2.28 M (75 % -> 63 % busy), but the executed instructions grow by ~40 % (index arithmetic, shuffles, STS/LDS)
+// and the two load -> shared -> sync -> read phases sit on the critical path of a warp: with 12 warps per SM (168
+// registers) the kernel is bound by latency per warp, not by the L1. Kept behind EDGE_STAGED=1 for the parity suite.
+#ifndef EDGE_STAGED
+#define EDGE_STAGED 0
+#endif
+// One load instruction takes G = 32 / REC whole records (lane = g * REC + c reads component c of record k * G + g), so
+// that every address is a per-lane base plus a compile-time offset; a record of the scratch is S = REC | 1 doubles
+// (odd: the per-lane record reads are conflict-free).
+template <int REC>
+struct StageRec {
+  static constexpr int S = REC | 1, SIZE = 32 * S, G = 32 / REC, NI = (32 + G - 1) / G;
+};
+template <int REC>
+__device__ __forceinline__ void stage_load(const double* __restrict__ base, int stride, int idx, double* tmp) {
+  using R = StageRec<REC>;
+  const int lane = threadIdx.x & 31, g = lane / REC, c = lane - g * REC;
+#pragma unroll
+  for (int k = 0; k < R::NI; ++k) {
+    const int r = k * R::G + g;
+    const int src = __shfl_sync(0xffffffffu, idx, r & 31);
+    if (g < R::G && r < 32) tmp[k] = __ldg(base + (size_t)src * stride + c);  // (stage_put has the same guard)
+  }
+}
+template <int REC>
+__device__ __forceinline__ void stage_put(double* sc, const double* tmp) {
+  using R = StageRec<REC>;
+  const int lane = threadIdx.x & 31, g = lane / REC, c = lane - g * REC;
+  double* mine = sc + g * R::S + c;
+#pragma unroll
+  for (int k = 0; k < R::NI; ++k)
+    if (g < R::G && k * R::G + g < 32) mine[k * R::G * R::S] = tmp[k];
+}
+template <int REC>
+__device__ __forceinline__ void stage_get(const double* sc, double* out) {
+  const double* mine = sc + (threadIdx.x & 31) * StageRec<REC>::S;
+#pragma unroll
+  for (int c = 0; c < REC; ++c) out[c] = mine[c];
 }
 
 // ------------------------------------------------------------------------------------------------
 // Roe + MUSCL (+ viscous) edge kernel
 // ------------------------------------------------------------------------------------------------
+// rows of a warp's tile beyond the two Jacobians: the mean viscous gradient of each edge when the gathers are staged
+template <int ND, bool VISC>
+static constexpr int edge_roe_extra_rows() { return EDGE_STAGED && VISC ? (ND + 1) * ND : 0; }
+
 template <int ND, bool VISC, bool COLORED>
 __global__ void __launch_bounds__(EDGE_BLOCK, EDGE_MIN_BLOCKS) k_edge_roe(EdgeArgs a, FlowParams p, int n) {
   using I = PrimIdx<ND>;
   constexpr int NV = ND + 2;
   constexpr int NP1 = VISC ? ND + 9 : ND + 4;  // gathered first-order primitives
+  constexpr int NGR = ND + 2;                  // reconstructed variables with gradients
   extern __shared__ double sjac[];
-  const SmemJac jac_i{sjac + threadIdx.x}, jac_j{sjac + NV * NV * JSTRIDE + threadIdx.x};
-  // EDGE_PER_THREAD edges per thread, one after the other: the indices of all of them are fetched first, and the
-  // point data of the next edge is pulled towards L1/L2 while the current one is computed (the kernel is bound by
-  // the latency of its gathers at 12 warps per SM, not by issue or bandwidth)
-  const int tbase = blockIdx.x * (EDGE_BLOCK * EDGE_PER_THREAD) + threadIdx.x;
-  int ee[EDGE_PER_THREAD], ii[EDGE_PER_THREAD], jj[EDGE_PER_THREAD], bbij[EDGE_PER_THREAD], bbji[EDGE_PER_THREAD];
-#pragma unroll
-  for (int q = 0; q < EDGE_PER_THREAD; ++q) {
-    const int tq = tbase + q * EDGE_BLOCK;
-    ee[q] = ii[q] = jj[q] = 0;
-    bbij[q] = bbji[q] = -1;
-    if (tq < n) {
-      ee[q] = COLORED ? a.color_edges[tq] : tq;
-      ii[q] = LD_ONCE(a.ei + ee[q]); jj[q] = LD_ONCE(a.ej + ee[q]);
-      bbij[q] = LD_ONCE(a.eij + ee[q]); bbji[q] = LD_ONCE(a.eji + ee[q]);  // used by the stores at the very end
-    }
-  }
-#pragma unroll
-  for (int q = 0; q < EDGE_PER_THREAD; ++q) {
-  const bool valid = tbase + q * EDGE_BLOCK < n;
-  const int e = ee[q], i = ii[q], j = jj[q], bij = bbij[q], bji = bbji[q];
-  if (q + 1 < EDGE_PER_THREAD && bbij[q + 1 < EDGE_PER_THREAD ? q + 1 : q] >= 0) {
-    const int qn = q + 1 < EDGE_PER_THREAD ? q + 1 : q;
-    prefetch_point<ND, VISC>(a, ii[qn]);
-    prefetch_point<ND, VISC>(a, jj[qn]);
+  constexpr int WT = (2 * NV * NV + edge_roe_extra_rows<ND, VISC>()) * JSTRIDE;
+  double* const wtile = sjac + (threadIdx.x >> 5) * WT;
+  const SmemJac jac_i{wtile + (threadIdx.x & 31)}, jac_j{wtile + NV * NV * JSTRIDE + (threadIdx.x & 31)};
+  const int t = blockIdx.x * EDGE_BLOCK + threadIdx.x;
+  const bool valid = t < n;
+  int e = 0, i = 0, j = 0, bij = -1, bji = -1;
+  if (valid) {
+    e = COLORED ? a.color_edges[t] : t;
+    i = LD_ONCE(a.ei + e); j = LD_ONCE(a.ej + e);
+    bij = LD_ONCE(a.eij + e); bji = LD_ONCE(a.eji + e);  // used by the stores at the very end
   }
   double flux[NV];
-  if (valid) {
   double normal[ND], vij[ND];
-#pragma unroll
-  for (int d = 0; d < ND; ++d) {
-    normal[d] = LD_ONCE(a.enormal + (size_t)d * a.E + e);
-    vij[d] = a.coord[(size_t)j * ND + d] - a.coord[(size_t)i * ND + d];
-  }
-  // (re-reading the point states for the viscous part instead of keeping them alive across the Roe flux was
-  //  measured slower: 2.09 ms vs 1.92 ms on 129^3)
   double Vi1[I::NPRIM], Vj1[I::NPRIM];
+#if EDGE_STAGED
+  double* const sc = wtile;  // the Jacobian rows of the tile are free until the flux is computed
+  const SmemJac gmean{wtile + 2 * NV * NV * JSTRIDE + (threadIdx.x & 31)};
+  // the viscous part wants the mean of the same gradients the reconstruction reads: form it while they are here
+  const bool mean_staged = VISC && p.muscl && a.grad_prim == a.grad_rec;
+  {
+    double tv[2][StageRec<NP1>::NI], tc[2][StageRec<ND>::NI];
+    stage_load<NP1>(a.V, I::NPRIM, i, tv[0]);
+    stage_load<NP1>(a.V, I::NPRIM, j, tv[1]);
+    stage_load<ND>(a.coord, ND, i, tc[0]);
+    stage_load<ND>(a.coord, ND, j, tc[1]);
+    constexpr int OV = StageRec<NP1>::SIZE, OC = StageRec<ND>::SIZE;
+    static_assert(2 * OV + 2 * OC <= 2 * NV * NV * JSTRIDE, "stage 1 exceeds the warp's Jacobian tile");
+    stage_put<NP1>(sc, tv[0]);
+    stage_put<NP1>(sc + OV, tv[1]);
+    stage_put<ND>(sc + 2 * OV, tc[0]);
+    stage_put<ND>(sc + 2 * OV + OC, tc[1]);
+    __syncwarp();
+    double ci[ND], cj[ND];
+    stage_get<NP1>(sc, Vi1);
+    stage_get<NP1>(sc + OV, Vj1);
+    stage_get<ND>(sc + 2 * OV, ci);
+    stage_get<ND>(sc + 2 * OV + OC, cj);
 #pragma unroll
-  for (int k = 0; k < NP1; ++k) {
-    Vi1[k] = a.V[(size_t)i * I::NPRIM + k];
-    Vj1[k] = a.V[(size_t)j * I::NPRIM + k];
+    for (int d = 0; d < ND; ++d) vij[d] = cj[d] - ci[d];
+    __syncwarp();
   }
-  double Vi[ND + 4], Vj[ND + 4];
+  double gi[NGR * ND], gj[NGR * ND], lim_i[NGR], lim_j[NGR];
   if (p.muscl) {
-    muscl_reconstruct<ND>(p, a, e, i, j, Vi1, Vj1, vij, Vi, Vj);
-  } else {
+    double tg[2][StageRec<NGR * ND>::NI], tl[2][StageRec<NGR>::NI];
+    stage_load<NGR * ND>(a.grad_rec, a.ngs * ND, i, tg[0]);
+    stage_load<NGR * ND>(a.grad_rec, a.ngs * ND, j, tg[1]);
+    if (p.limiter) {
+      stage_load<NGR>(a.limiter, NGR, i, tl[0]);
+      stage_load<NGR>(a.limiter, NGR, j, tl[1]);
+    }
+    constexpr int OG = StageRec<NGR * ND>::SIZE, OL = StageRec<NGR>::SIZE;
+    static_assert(2 * OG + 2 * OL <= 2 * NV * NV * JSTRIDE, "stage 2 exceeds the warp's Jacobian tile");
+    stage_put<NGR * ND>(sc, tg[0]);
+    stage_put<NGR * ND>(sc + OG, tg[1]);
+    if (p.limiter) {
+      stage_put<NGR>(sc + 2 * OG, tl[0]);
+      stage_put<NGR>(sc + 2 * OG + OL, tl[1]);
+    }
+    __syncwarp();
+    stage_get<NGR * ND>(sc, gi);
+    stage_get<NGR * ND>(sc + OG, gj);
+    if (p.limiter) {
+      stage_get<NGR>(sc + 2 * OG, lim_i);
+      stage_get<NGR>(sc + 2 * OG + OL, lim_j);
+    }
+    __syncwarp();
+    if (mean_staged) {
 #pragma unroll
-    for (int k = 0; k < ND + 4; ++k) { Vi[k] = Vi1[k]; Vj[k] = Vj1[k]; }
+      for (int k = 0; k < (ND + 1) * ND; ++k) {  // the expression of viscous_terms
+        double m = gi[k];
+        m *= 0.5;
+        m += 0.5 * gj[k];
+        gmean[k] = m;
+      }
+    }
   }
-  roe_flux<ND, true>(p, Vi, Vj, normal, flux, jac_i, jac_j);
-  if (VISC) {
-    const double area = sqrt(dotN<ND>(normal, normal));
-    double un[ND];
+#else
+  const double *gi = nullptr, *gj = nullptr, *lim_i = nullptr, *lim_j = nullptr;
+  const bool mean_staged = false;
+  const SmemJac gmean{wtile};
+  if (valid) {
 #pragma unroll
-    for (int d = 0; d < ND; ++d) un[d] = normal[d] / area;
-    viscous_terms<ND, true, false>(p, Vi1, Vj1, a.grad_prim + (size_t)i * a.ngs * ND,
-                                   a.grad_prim + (size_t)j * a.ngs * ND, vij, area, un, true, flux, jac_i, jac_j);
+    for (int d = 0; d < ND; ++d) vij[d] = a.coord[(size_t)j * ND + d] - a.coord[(size_t)i * ND + d];
+#pragma unroll
+    for (int k = 0; k < NP1; ++k) {
+      Vi1[k] = a.V[(size_t)i * I::NPRIM + k];
+      Vj1[k] = a.V[(size_t)j * I::NPRIM + k];
+    }
+    gi = a.grad_rec + (size_t)i * a.ngs * ND;
+    gj = a.grad_rec + (size_t)j * a.ngs * ND;
+    lim_i = a.limiter + (size_t)i * NGR;
+    lim_j = a.limiter + (size_t)j * NGR;
   }
+#endif
+  if (valid) {
+#pragma unroll
+    for (int d = 0; d < ND; ++d) normal[d] = LD_ONCE(a.enormal + (size_t)d * a.E + e);
+    double Vi[ND + 4], Vj[ND + 4];
+    if (p.muscl) {
+      muscl_reconstruct<ND>(p, a, e, gi, gj, lim_i, lim_j, Vi1, Vj1, vij, Vi, Vj);
+    } else {
+#pragma unroll
+      for (int k = 0; k < ND + 4; ++k) { Vi[k] = Vi1[k]; Vj[k] = Vj1[k]; }
+    }
+    roe_flux<ND, true>(p, Vi, Vj, normal, flux, jac_i, jac_j);
+    if (VISC) {
+      const double area = sqrt(dotN<ND>(normal, normal));
+      double un[ND];
+#pragma unroll
+      for (int d = 0; d < ND; ++d) un[d] = normal[d] / area;
+      viscous_terms<ND, true, false>(p, Vi1, Vj1, a.grad_prim + (size_t)i * a.ngs * ND,
+                                     a.grad_prim + (size_t)j * a.ngs * ND, vij, area, un, true, flux, jac_i, jac_j,
+                                     mean_staged, gmean);
+    }
   }  // valid
-  store_edge_outputs<ND, COLORED>(a, valid, e, i, j, bij, bji, flux, jac_i, jac_j, sjac);
-  __syncwarp();  // the warp has read this pass's blocks before the next pass overwrites them
-  }  // q
+  store_edge_outputs<ND, COLORED>(a, valid, e, i, j, bij, bji, flux, jac_i, jac_j, wtile);
 }
 
 // ------------------------------------------------------------------------------------------------
@@ -275,7 +367,8 @@ __global__ void __launch_bounds__(EDGE_BLOCK, EDGE_MIN_BLOCKS) k_edge_jst(EdgeAr
   constexpr int NV = ND + 2;
   constexpr int NP1 = VISC ? ND + 9 : ND + 5;
   extern __shared__ double sjac[];
-  const SmemJac jac_i{sjac + threadIdx.x}, jac_j{sjac + NV * NV * JSTRIDE + threadIdx.x};
+  double* const wtile = sjac + (threadIdx.x >> 5) * (2 * NV * NV * JSTRIDE);
+  const SmemJac jac_i{wtile + (threadIdx.x & 31)}, jac_j{wtile + NV * NV * JSTRIDE + (threadIdx.x & 31)};
   const int t = blockIdx.x * blockDim.x + threadIdx.x;
   const bool valid = t < n;
   int e = 0, i = 0, j = 0, bij = -1, bji = -1;
@@ -347,13 +440,16 @@ __global__ void __launch_bounds__(EDGE_BLOCK, EDGE_MIN_BLOCKS) k_edge_jst(EdgeAr
                                    a.grad_prim + (size_t)j * a.ngs * ND, vij, area, un, true, flux, jac_i, jac_j);
   }
   }  // valid
-  store_edge_outputs<ND, COLORED>(a, valid, e, i, j, bij, bji, flux, jac_i, jac_j, sjac);
+  store_edge_outputs<ND, COLORED>(a, valid, e, i, j, bij, bji, flux, jac_i, jac_j, wtile);
 }
 
 // ------------------------------------------------------------------------------------------------
 // Point gather: residual = signed sum of edge fluxes, diagonal block = -(column sum of off-diagonals).
 // One warp-lane per (point); loops over the neighbour CSR (ascending edge index == reference order of
 // CPoint::Edge, which is built in edge-creation order).
+// (A warp-per-32-points form -- 25 lanes on one contiguous block, 5 lanes on the flux, walking the warp's CSR range
+//  with 8 loads in flight -- cut the L1 wavefronts 10x but serialises the warp's ~190 entries: 6.3 ms against 2.85 ms
+//  on 185^3. The kernel lives on the memory parallelism of 32 independent points per warp, so it stays as it is.)
 // ------------------------------------------------------------------------------------------------
 template <int NV>
 __global__ void k_point_sum(int P, int E, const int* __restrict__ nbr_ptr, const int* __restrict__ gat_edge,
@@ -434,9 +530,11 @@ static void launch_edge(su2b200_ctx* c, const EdgeArgs& a, const FlowParams& p, 
     if (visc) { if (colored) SU2B_EDGE(k_edge_jst, true, true, 1); else SU2B_EDGE(k_edge_jst, true, false, 1); }
     else { if (colored) SU2B_EDGE(k_edge_jst, false, true, 1); else SU2B_EDGE(k_edge_jst, false, false, 1); }
   } else {
-    constexpr int EPT = EDGE_PER_THREAD;
-    if (visc) { if (colored) SU2B_EDGE(k_edge_roe, true, true, EPT); else SU2B_EDGE(k_edge_roe, true, false, EPT); }
-    else { if (colored) SU2B_EDGE(k_edge_roe, false, true, EPT); else SU2B_EDGE(k_edge_roe, false, false, EPT); }
+#define SU2B_EDGE_ROE(V, C) \
+  launch_edge_kernel(c, k_edge_roe<ND, V, C>, edge_smem_bytes<ND + 2>(edge_roe_extra_rows<ND, V>()), a, p, n, 1)
+    if (visc) { if (colored) SU2B_EDGE_ROE(true, true); else SU2B_EDGE_ROE(true, false); }
+    else { if (colored) SU2B_EDGE_ROE(false, true); else SU2B_EDGE_ROE(false, false); }
+#undef SU2B_EDGE_ROE
   }
 #undef SU2B_EDGE
 }
