@@ -392,8 +392,11 @@ __device__ __forceinline__ bool is_sentinel(double v) {
   return (unsigned)__double2hiint(v) == (unsigned)(SENTINEL >> 32);
 }
 
+#ifndef FACTOR_ROWS_MIN_BLOCKS
+#define FACTOR_ROWS_MIN_BLOCKS 3  // resident blocks per SM the register allocation aims at
+#endif
 template <int NV>
-__global__ void __launch_bounds__(128) k_factor_rows(int nGroups, int slim, int ownCap, int srcCap, const RowDesc* __restrict__ desc,
+__global__ void __launch_bounds__(128, FACTOR_ROWS_MIN_BLOCKS) k_factor_rows(int nGroups, int slim, int ownCap, int srcCap, const RowDesc* __restrict__ desc,
                                                      const int2* __restrict__ ops, int* ctrl,
                                                      const int* __restrict__ col_ind, const double* __restrict__ A,
                                                      double* ILU, double* invM) {
@@ -827,7 +830,8 @@ static void factor_launch_rows(su2b200_ctx* c, LinSys& ls, int gbeg, int gend) {
   SU2B_CUDA(cudaGetDevice(&dev));
   SU2B_CUDA(cudaDeviceGetAttribute(&nsm, cudaDevAttrMultiProcessorCount, dev));
   SU2B_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&perSm, k_factor_rows<NV>, 128, smem));
-  static const int capR = getenv("SU2B200_FACTOR_ROWS_BLOCKS") ? atoi(getenv("SU2B200_FACTOR_ROWS_BLOCKS")) : 3;
+  static const int capR =
+      getenv("SU2B200_FACTOR_ROWS_BLOCKS") ? atoi(getenv("SU2B200_FACTOR_ROWS_BLOCKS")) : FACTOR_ROWS_MIN_BLOCKS;
   if (capR > 0) perSm = std::min(perSm, capR);
   SU2B_REQUIRE(perSm > 0, "ilu factor (rows) kernel does not fit an SM");
   int nGroups = gend - gbeg;
