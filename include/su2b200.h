@@ -153,6 +153,12 @@ int su2b200_mesh_create_box(int nDim, const unsigned long n[3], const double len
                             int rank, int nranks, int tets, su2b200_mesh** out);
 /* MESH_FORMAT= SU2 (CSU2ASCIIMeshReaderBase.cpp): NDIME / NELEM / NPOIN / NMARK blocks, VTK element ids */
 int su2b200_mesh_read_su2(const char* path, su2b200_mesh** out);
+/* .su2 ASCII writer, the inverse of su2b200_mesh_read_su2 (same blocks; layout of QuickStart/mesh_NACA0012_inv.su2:1-5):
+ * how the tetrahedral and the stretched synthetic boxes reach the reference for the parity fixtures (SURVEY 8(d)(3,4)) */
+int su2b200_mesh_write_su2(su2b200_mesh* mesh, const char* path);
+/* geometric stretching of a BOX/RECTANGLE mesh along `axis` before preprocessing: cell sizes first_cell, first_cell*ratio,
+ * ... from the minus side, rescaled to the box length (the stretched wall-normal spacing of the "wing-box" input) */
+int su2b200_mesh_stretch(su2b200_mesh* mesh, int axis, double first_cell, double ratio);
 int su2b200_mesh_destroy(su2b200_mesh* mesh);
 /* MARKER_EULER / MARKER_FAR / MARKER_SYM / MARKER_HEATFLUX + MARKER_MONITORING of the cfg file */
 int su2b200_mesh_set_marker(su2b200_mesh* mesh, const char* tag, int kindBC, int monitoring, double heat_flux);

@@ -167,7 +167,7 @@ def flow_config_from_cfg(opts, nDim):
     return kw
 
 
-def mesh_from_cfg(opts, rank=0, nranks=1, base_dir="."):
+def mesh_from_cfg(opts, rank=0, nranks=1, base_dir=".", rcm=True, tets=False, stretch=None):
     """MESH_FORMAT= BOX / RECTANGLE / SU2 -> preprocessed su2_b200.mesh.Mesh with the cfg's boundary conditions."""
     import os
     from .mesh import Mesh
@@ -179,7 +179,9 @@ def mesh_from_cfg(opts, rank=0, nranks=1, base_dir="."):
         n = [int(float(x)) for x in _list(o["MESH_BOX_SIZE"])][:nd]
         ln = [float(x) for x in _list(o["MESH_BOX_LENGTH"])][:nd]
         of = [float(x) for x in _list(o["MESH_BOX_OFFSET"])][:nd]
-        m = Mesh.box(n, ln, of, rank=rank, nranks=nranks)
+        m = Mesh.box(n, ln, of, rank=rank, nranks=nranks, tets=tets)
+        if stretch:
+            m.stretch(*stretch)
     elif fmt == "SU2":
         if nranks != 1:
             raise ValueError("partitioned .su2 meshes are not supported yet (BOX/RECTANGLE only)")
@@ -188,5 +190,7 @@ def mesh_from_cfg(opts, rank=0, nranks=1, base_dir="."):
         raise ValueError("MESH_FORMAT= %s not supported" % fmt)
     for tag, (kind, mon, q) in markers_from_cfg(o).items():
         m.set_marker(tag, kind, mon, q)
-    m.preprocess(rcm=(fmt == "SU2"))
+    # the reference RCM-orders every mesh, generated boxes included (CPhysicalGeometry.cpp:4478, called from
+    # CDriver::InitializeGeometryFVM): the ILU(0) factors depend on the ordering, so the default follows it
+    m.preprocess(rcm=rcm)
     return m

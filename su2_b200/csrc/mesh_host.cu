@@ -402,12 +402,77 @@ void build_neighbours(const su2b200_mesh& m, std::vector<long>& ptr, std::vector
   }
 }
 
+// Local node adjacency of an element (the nodes that share an element edge with local node k), listed in the order of
+// the reference's primal-grid classes (C<Elem>Connectivity::Neighbor_Nodes, Common/include/geometry/primal_grid/*.hpp):
+// that order decides the order of CPoint::Point, hence the RCM tie-breaking and the edge numbering.
+struct NodeAdj { int cnt[8]; int adj[8][4]; };
+static const NodeAdj& node_adjacency(int vtk) {
+  static const NodeAdj tri = {{2, 2, 2}, {{1, 2}, {2, 0}, {0, 1}}};
+  static const NodeAdj quad = {{2, 2, 2, 2}, {{1, 3}, {2, 0}, {3, 1}, {0, 2}}};
+  static const NodeAdj tet = {{3, 3, 3, 3}, {{1, 2, 3}, {0, 2, 3}, {0, 1, 3}, {0, 1, 2}}};
+  static const NodeAdj hex = {{3, 3, 3, 3, 3, 3, 3, 3},
+                              {{1, 3, 4}, {0, 2, 5}, {1, 3, 6}, {0, 2, 7}, {0, 5, 7}, {4, 6, 1}, {2, 5, 7}, {4, 3, 6}}};
+  static const NodeAdj prism = {{3, 3, 3, 3, 3, 3}, {{1, 2, 3}, {0, 2, 4}, {1, 0, 5}, {0, 4, 5}, {3, 5, 1}, {4, 3, 2}}};
+  static const NodeAdj pyra = {{3, 3, 3, 3, 4}, {{1, 3, 4}, {0, 2, 4}, {1, 3, 4}, {2, 0, 4}, {0, 1, 2, 3}}};
+  switch (vtk) {
+    case VTK_TRI: return tri;
+    case VTK_QUAD: return quad;
+    case VTK_TET: return tet;
+    case VTK_HEX: return hex;
+    case VTK_PRISM: return prism;
+    case VTK_PYRAMID: return pyra;
+    default: throw Error("unsupported volume element type " + std::to_string(vtk));
+  }
+}
+
+// Neighbours of every point in the order CPhysicalGeometry::SetPoint_Connectivity (CPhysicalGeometry.cpp:4417-4476)
+// finds them: elements of the point by ascending element index, within an element the adjacency listing above, first
+// occurrence wins. Same sets (and the same halo-halo exclusion) as build_neighbours, so `ptr` is shared.
+void build_neighbours_elem_order(const su2b200_mesh& m, const std::vector<long>& ptr, std::vector<int>& rnbr) {
+  const long P = m.P;
+  std::vector<long> eptr(P + 1, 0);
+  for (int n : m.enode) eptr[n + 1]++;
+  for (long i = 0; i < P; ++i) eptr[i + 1] += eptr[i];
+  std::vector<int> pel(eptr[P]);
+  {
+    std::vector<long> pos(eptr.begin(), eptr.end() - 1);
+    for (long e = 0; e < m.nElem(); ++e)
+      for (long q = m.eptr[e]; q < m.eptr[e + 1]; ++q) pel[pos[m.enode[q]]++] = (int)e;
+  }
+  rnbr.assign(ptr[P], -1);
+  for (long i = 0; i < P; ++i) {
+    long w = ptr[i];
+    for (long q = eptr[i]; q < eptr[i + 1]; ++q) {
+      const int e = pel[q];
+      const int* nd = &m.enode[m.eptr[e]];
+      const NodeAdj& na = node_adjacency(m.etype[e]);
+      const int nn = (int)(m.eptr[e + 1] - m.eptr[e]);
+      for (int k = 0; k < nn; ++k) {
+        if (nd[k] != i) continue;
+        for (int a = 0; a < na.cnt[k]; ++a) {
+          const int j = nd[na.adj[k][a]];
+          if (i >= m.Pd && j >= m.Pd) continue;
+          if (std::find(rnbr.begin() + ptr[i], rnbr.begin() + w, j) == rnbr.begin() + w) {
+            SU2B_REQUIRE(w < ptr[i + 1], "inconsistent neighbour lists");
+            rnbr[w++] = j;
+          }
+        }
+      }
+    }
+    SU2B_REQUIRE(w == ptr[i + 1], "inconsistent neighbour lists");
+  }
+}
+
 // Reverse Cuthill-McKee over the owned points (halos keep their place after them): BFS from a minimum-degree seed,
 // neighbours visited by ascending degree, order reversed -- the recipe of CPhysicalGeometry::SetRCM_Ordering.
 void rcm_reorder(su2b200_mesh& m) {
   std::vector<long> ptr;
   std::vector<int> nbr;
-  build_neighbours(m, ptr, nbr);
+  {
+    std::vector<int> asc;
+    build_neighbours(m, ptr, asc);
+    build_neighbours_elem_order(m, ptr, nbr);  // the reference walks CPoint::Point, which is in this order
+  }
   const long Pd = m.Pd, P = m.P;
   auto degree = [&](long i) { return ptr[i + 1] - ptr[i]; };
   std::vector<char> seen(P, 0);
@@ -547,7 +612,14 @@ void preprocess(su2b200_mesh& m, int rcm) {
   std::vector<long> ptr;
   std::vector<int> nbr;
   build_neighbours(m, ptr, nbr);
-  // ---- edges: (i, j) with i < j, ordered by i then j (SetEdges creates them while sweeping the points) ----
+  // ---- edges: (i, j) with i < j, numbered as CGeometry::SetEdges (CGeometry.cpp:1263-1293) does: points ascending,
+  // within a point its neighbours in CPoint::Point order (element order, see build_neighbours_elem_order) ----
+  std::vector<int> rnbr;
+  build_neighbours_elem_order(m, ptr, rnbr);
+  auto asc_pos = [&](long a, long b) -> long {
+    const long k = std::lower_bound(nbr.begin() + ptr[a], nbr.begin() + ptr[a + 1], (int)b) - nbr.begin();
+    return (k < ptr[a + 1] && nbr[k] == b) ? k : -1;
+  };
   long E = 0;
   for (long i = 0; i < P; ++i)
     for (long k = ptr[i]; k < ptr[i + 1]; ++k) E += nbr[k] > i;
@@ -555,26 +627,27 @@ void preprocess(su2b200_mesh& m, int rcm) {
   m.edge_n0.resize(E);
   m.edge_n1.resize(E);
   m.point_ptr.assign(ptr.begin(), ptr.end());
-  m.point_nbr.assign(nbr.begin(), nbr.end());
+  m.point_nbr.assign(rnbr.begin(), rnbr.end());
   m.point_edge.assign(nbr.size(), 0);
+  std::vector<long> asc_edge(nbr.size(), -1);  // edge of the k-th entry of the ascending neighbour lists
   {
     long e = 0;
     for (long i = 0; i < P; ++i)
       for (long k = ptr[i]; k < ptr[i + 1]; ++k) {
-        const long j = nbr[k];
+        const long j = rnbr[k];
         if (j < i) continue;
         m.edge_n0[e] = (ulong_t)i;
         m.edge_n1[e] = (ulong_t)j;
-        m.point_edge[k] = (ulong_t)e;
-        // position of i in j's (ascending) list: entries < j come first and are filled in order of i
-        const long kk = std::lower_bound(nbr.begin() + ptr[j], nbr.begin() + ptr[j + 1], (int)i) - nbr.begin();
-        m.point_edge[kk] = (ulong_t)e;
+        asc_edge[asc_pos(i, j)] = e;
+        asc_edge[asc_pos(j, i)] = e;
         ++e;
       }
+    for (long i = 0; i < P; ++i)
+      for (long k = ptr[i]; k < ptr[i + 1]; ++k) m.point_edge[k] = (ulong_t)asc_edge[asc_pos(i, rnbr[k])];
   }
   auto find_edge = [&](int a, int b) -> long {
-    const long k = std::lower_bound(nbr.begin() + ptr[a], nbr.begin() + ptr[a + 1], b) - nbr.begin();
-    return (k < ptr[a + 1] && nbr[k] == b) ? (long)m.point_edge[k] : -1;
+    const long k = asc_pos(a, b);
+    return k >= 0 ? asc_edge[k] : -1;
   };
   // ---- median-dual control volumes ----
   m.edge_normal.assign((size_t)E * D, 0.0);
@@ -701,9 +774,9 @@ void preprocess(su2b200_mesh& m, int rcm) {
       for (int d = 0; d < D; ++d) mk.vunit[v * D + d] = nv[d] / area;
       // FindNormal_Neighbor: neighbour best aligned with the (inward) normal
       double cosmax = -1.0;
-      long best = ptr[i + 1] > ptr[i] ? nbr[ptr[i]] : i;
+      long best = ptr[i + 1] > ptr[i] ? rnbr[ptr[i]] : i;
       for (long q = ptr[i]; q < ptr[i + 1]; ++q) {
-        const long j = nbr[q];
+        const long j = rnbr[q];  // CPoint::Point order: the last neighbour that reaches the maximum wins
         double sp = 0, nv2 = 0;
         for (int d = 0; d < D; ++d) { const double dc = X(m, j)[d] - X(m, i)[d]; sp += dc * nv[d]; nv2 += dc * dc; }
         const double ca = sp / (std::sqrt(nv2) * area);
@@ -765,7 +838,7 @@ void preprocess(su2b200_mesh& m, int rcm) {
   for (long i = 0; i < P; ++i)
     for (long k = ptr[i]; k < ptr[i + 1]; ++k) {
       const long j = nbr[k];
-      const long e = (long)m.point_edge[k];
+      const long e = asc_edge[k];
       // block (i, j): position of j within row i = k - ptr[i] (+1 if the diagonal precedes it)
       const ulong_t posn = m.row_ptr[i] + (ulong_t)(k - ptr[i]) + (j > i ? 1 : 0);
       if (i < j) m.edge_ptr[2 * (size_t)e] = posn; else m.edge_ptr[2 * (size_t)e + 1] = posn;
@@ -803,6 +876,59 @@ void preprocess(su2b200_mesh& m, int rcm) {
   m.preprocessed = true;
 }
 
+// ---- .su2 ASCII writer (format of CSU2ASCIIMeshReaderBase.cpp: NDIME / NELEM / NPOIN / NMARK blocks, VTK type ids;
+// layout as in QuickStart/mesh_NACA0012_inv.su2). Writes the mesh in its current numbering; serial meshes only. ----
+void write_su2(const su2b200_mesh& m, const char* path) {
+  SU2B_REQUIRE(m.nranks == 1, "only undivided meshes can be written");
+  FILE* f = std::fopen(path, "w");
+  if (!f) throw Error(std::string("cannot open ") + path + " for writing");
+  std::fprintf(f, "NDIME= %d\nNELEM= %ld\n", m.nDim, m.nElem());
+  for (long e = 0; e < m.nElem(); ++e) {
+    std::fprintf(f, "%d", m.etype[e]);
+    for (long q = m.eptr[e]; q < m.eptr[e + 1]; ++q) std::fprintf(f, "\t%d", m.enode[q]);
+    std::fprintf(f, "\t%ld\n", e);
+  }
+  std::fprintf(f, "NPOIN= %ld\n", m.P);
+  for (long i = 0; i < m.P; ++i) {
+    for (int d = 0; d < m.nDim; ++d) std::fprintf(f, "%.17g\t", m.coord[(size_t)i * m.nDim + d]);
+    std::fprintf(f, "%ld\n", i);
+  }
+  std::fprintf(f, "NMARK= %zu\n", m.markers.size());
+  for (const auto& mk : m.markers) {
+    std::fprintf(f, "MARKER_TAG= %s\nMARKER_ELEMS= %zu\n", mk.tag.c_str(), mk.etype.size());
+    for (size_t b = 0; b < mk.etype.size(); ++b) {
+      std::fprintf(f, "%d", mk.etype[b]);
+      for (long q = mk.eptr[b]; q < mk.eptr[b + 1]; ++q) std::fprintf(f, "\t%d", mk.enode[q]);
+      std::fprintf(f, "\n");
+    }
+  }
+  std::fclose(f);
+}
+
+// Geometric stretching of a structured box along one axis (the "wing-box" input of SURVEY 8(d)(4): wall-normal spacing
+// first_cell, first_cell*ratio, ... from the minus side, rescaled to the box length). Coordinates only.
+void stretch_axis(su2b200_mesh& m, int axis, double first_cell, double ratio) {
+  SU2B_REQUIRE(m.is_box && !m.preprocessed, "stretching applies to BOX/RECTANGLE meshes before preprocessing");
+  SU2B_REQUIRE(axis >= 0 && axis < m.nDim && first_cell > 0.0 && ratio > 0.0, "invalid stretching parameters");
+  const double L = m.box_len[axis], o = m.box_off[axis];
+  // number of cells along the axis from the uniform spacing of the generator
+  double hmin = L;
+  for (long i = 0; i < m.P; ++i) {
+    const double x = m.coord[(size_t)i * m.nDim + axis] - o;
+    if (x > 1e-14 * L && x < hmin) hmin = x;
+  }
+  const long nc = std::lround(L / hmin);
+  std::vector<double> y(nc + 1, 0.0);
+  double h = first_cell;
+  for (long k = 1; k <= nc; ++k) { y[k] = y[k - 1] + h; h *= ratio; }
+  for (long k = 0; k <= nc; ++k) y[k] *= L / y[nc];
+  for (long i = 0; i < m.P; ++i) {
+    double& x = m.coord[(size_t)i * m.nDim + axis];
+    const long k = std::lround((x - o) / hmin);
+    x = o + y[std::min(std::max(k, 0L), nc)];
+  }
+}
+
 }  // namespace
 
 #define API_BEGIN try {
@@ -832,6 +958,20 @@ int su2b200_mesh_read_su2(const char* path, su2b200_mesh** out) {
   API_BEGIN
   SU2B_REQUIRE(out && path, "null argument");
   *out = read_su2(path);
+  API_END
+}
+
+int su2b200_mesh_write_su2(su2b200_mesh* m, const char* path) {
+  API_BEGIN
+  SU2B_REQUIRE(m && path, "null argument");
+  write_su2(*m, path);
+  API_END
+}
+
+int su2b200_mesh_stretch(su2b200_mesh* m, int axis, double first_cell, double ratio) {
+  API_BEGIN
+  SU2B_REQUIRE(m, "null mesh");
+  stretch_axis(*m, axis, first_cell, ratio);
   API_END
 }
 

@@ -35,6 +35,14 @@ class Mesh:
         check(lib.su2b200_mesh_read_su2(str(path).encode(), C.byref(h)))
         return cls(h)
 
+    def write_su2(self, path):
+        """ASCII .su2 file of the mesh in its current numbering (su2b200_mesh_write_su2)."""
+        check(self.lib.su2b200_mesh_write_su2(self.h, str(path).encode()))
+
+    def stretch(self, axis, first_cell, ratio):
+        """Geometric wall-normal stretching of a box mesh before preprocess() (su2b200_mesh_stretch)."""
+        check(self.lib.su2b200_mesh_stretch(self.h, int(axis), C.c_double(first_cell), C.c_double(ratio)))
+
     def close(self):
         if self.h:
             self.lib.su2b200_mesh_destroy(self.h)

@@ -141,6 +141,58 @@ def test_generated_mesh_matches_reference_dual_grid(case):
     m.close()
 
 
+PINNED = ["naca0012_roe", "box_euler", "rect_ns", "box_rans_sa"]
+
+
+@pytest.mark.parametrize("case", PINNED)
+def test_own_geometry_path_reproduces_the_reference_numbering(case):
+    """Mesh reader / generator + RCM + dual grid against the reference's dump INDEX BY INDEX: the point permutation of
+    SetRCM_Ordering (CPhysicalGeometry.cpp:4478-4621), the edge numbering of SetEdges (CGeometry.cpp:1263), CPoint::Point
+    / CPoint::Edge in the reference's order, the sparse pattern and the edge -> block map, normals and volumes."""
+    gold = load_golden(os.path.join(ROOT, "tests", "golden", case + ".npz"))
+    opts = parse_cfg(open(os.path.join(ROOT, "tests", "cases", case + ".cfg")).read())
+    m = mesh_from_cfg(opts, base_dir="/root/reference/QuickStart" if case.startswith("naca") else ".") \
+        if (not case.startswith("naca") or os.path.isdir("/root/reference/QuickStart")) else None
+    if m is None:
+        pytest.skip("QuickStart mesh not on this machine")
+    E = int(gold["nEdge"])
+    assert np.array_equal(m.array("global_index").astype(np.int64), np.asarray(gold["global_index"]).astype(np.int64))
+    en = np.asarray(gold["edge_nodes"]).reshape(2, E)
+    assert np.array_equal(m.array("edge_node0"), en[0]) and np.array_equal(m.array("edge_node1"), en[1])
+    for k in ("point_ptr", "point_nbr", "point_edge", "row_ptr", "col_ind", "dia_ptr", "edge_ptr", "nNeighbor"):
+        assert np.array_equal(m.array(k).astype(np.int64), np.asarray(gold[k]).ravel().astype(np.int64)), k
+    scale = np.max(np.abs(gold["edge_normal"]))
+    assert np.max(np.abs(m.array("edge_normal") - np.asarray(gold["edge_normal"]).ravel())) <= 1e-13 * scale
+    assert np.allclose(m.array("volume"), gold["volume"], rtol=1e-11, atol=0)  # sums of up to 8 sub-volumes, other order
+    assert np.allclose(m.array("coord"), np.asarray(gold["coord"]).ravel(), rtol=0, atol=1e-15)
+    m.close()
+
+
+def test_su2_writer_round_trip(tmp_path):
+    """su2b200_mesh_write_su2 -> su2b200_mesh_read_su2 gives the same dual grid (tetrahedral and stretched boxes)."""
+    tags = ("x_minus", "x_plus", "y_minus", "y_plus", "z_minus", "z_plus")
+    for tets, stretch in ((True, None), (False, (1, 1e-3, 1.2))):
+        a = Mesh.box([5, 6, 4], [2.0, 1.0, 1.0], tets=tets)
+        if stretch:
+            a.stretch(*stretch)
+        path = tmp_path / ("box_%d.su2" % tets)
+        a.write_su2(path)
+        b = Mesh.read_su2(path)
+        for m in (a, b):
+            for t in tags:
+                m.set_marker(t, capi.FAR_FIELD)
+            m.preprocess(rcm=True)
+        assert a.sizes() == b.sizes()
+        for k in ("coord", "volume", "edge_normal", "edge_node0", "edge_node1", "col_ind", "edge_ptr", "global_index"):
+            assert np.array_equal(a.array(k), b.array(k)), k
+        if stretch:
+            y = np.unique(np.round(a.array("coord").reshape(-1, 3)[:, 1], 12))
+            d = np.diff(y)
+            assert np.allclose(d[1:] / d[:-1], 1.2, rtol=1e-9) and abs(y[-1] - 1.0) < 1e-12
+        a.close()
+        b.close()
+
+
 def test_sparse_pattern_and_edge_map_are_consistent():
     m = Mesh.box([7, 6, 5], [1.0, 1.0, 1.0])
     for tag in ("x_minus", "x_plus", "y_minus", "y_plus", "z_minus", "z_plus"):
