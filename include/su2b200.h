@@ -304,6 +304,15 @@ int su2b200_linsys_set_partitions(su2b200_ctx* ctx, int which, int nparts);
  * (default); build_mode: 0 one launch per level, 1 flag sweep, 2 single-launch polling factorisation (default).
  * All schedules perform the arithmetic of CSysMatrix.cpp:673-823 in the same order. */
 int su2b200_linsys_set_schedule(su2b200_ctx* ctx, int which, int apply_mode, int build_mode);
+/* level width (rows) from which the hybrid ILU0 schedules hand a level to the nVar-lanes-per-row kernels (default 4096
+ * for both): sweep_rows for the application, factor_rows for the factorisation; factor_mode 0 = warp-per-row kernel only,
+ * 1 = hybrid, 2 = rows kernel only; values <= 0 (factor_mode < 0) keep the current setting. Same arithmetic either way:
+ * the tests run the wide-level kernels on small meshes through this. */
+int su2b200_linsys_set_wide_threshold(su2b200_ctx* ctx, int which, int sweep_rows, int factor_rows, int factor_mode);
+/* explicit row partitions of the block-Jacobi preconditioner: first_row[nparts+1], first_row[0] = 0,
+ * first_row[nparts] = nPointDomain. The reference's omp_partitions (CSysMatrix.cpp:199-227) with caller-chosen
+ * boundaries; used to reproduce on one GPU the operator N ranks build (partitions = the ranks' row ranges). */
+int su2b200_linsys_set_partition_rows(su2b200_ctx* ctx, int which, int nparts, const unsigned long* first_row);
 /* CSysMatrix::HtDTransfer (CSysMatrixGPU.cu:59-64) */
 int su2b200_linsys_set_matrix(su2b200_ctx* ctx, int which, const double* blocks);
 /* CSysMatrix::GPUMatrixVectorProduct (CSysMatrixGPU.cu:66-86) == MatrixVectorProduct (CSysMatrix.cpp:617-645):
@@ -323,7 +332,8 @@ int su2b200_vector_dot(su2b200_ctx* ctx, int which, const double* a, const doubl
 /* 128-byte ncclUniqueId: rank 0 creates it, the host side broadcasts it (MPI_Bcast / torch.distributed) */
 int su2b200_comm_unique_id(unsigned char id[128]);
 int su2b200_comm_init(su2b200_ctx* ctx, int rank, int size, const unsigned char id[128]);
-/* halo exchange of a named array (MPI_QUANTITIES: SOLUTION, PRIMITIVE_GRADIENT, ...) */
+/* halo exchange of a named per-point array (MPI_QUANTITIES: SOLUTION, PRIMITIVE_GRADIENT, PRIMITIVE_LIMITER, ...):
+ * InitiateComms + CompleteComms in one call; count per point = su2b200_array_size / nPoint; no-op on a single rank */
 int su2b200_halo_exchange(su2b200_ctx* ctx, int which_array);
 
 /* ---- timing helpers used by bench.py (CUDA events on the context's compute stream) ----------- */

@@ -94,7 +94,8 @@ EXPORTED_SYMBOLS = [
     "su2b200_flow_forces", "su2b200_turb_preprocessing", "su2b200_turb_set_time_step",
     "su2b200_turb_space_integration", "su2b200_turb_prepare_implicit", "su2b200_turb_linear_solve",
     "su2b200_turb_complete_implicit", "su2b200_turb_postprocessing", "su2b200_iterate", "su2b200_linsys_create",
-    "su2b200_linsys_set_partitions", "su2b200_linsys_set_schedule", "su2b200_linsys_set_matrix", "su2b200_linsys_spmv",
+    "su2b200_linsys_set_partitions", "su2b200_linsys_set_schedule", "su2b200_linsys_set_wide_threshold",
+    "su2b200_linsys_set_partition_rows", "su2b200_linsys_set_matrix", "su2b200_linsys_spmv",
     "su2b200_linsys_build_preconditioner", "su2b200_linsys_apply_preconditioner", "su2b200_linsys_solve",
     "su2b200_vector_dot", "su2b200_comm_unique_id", "su2b200_comm_init", "su2b200_halo_exchange",
     "su2b200_timer_start", "su2b200_timer_stop", "su2b200_launch_count", "su2b200_bench_edge_kernel",

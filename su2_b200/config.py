@@ -63,6 +63,14 @@ def markers_from_cfg(opts):
     return out
 
 
+def _ref_elem_length(o):
+    if o.get("SYSTEM_MEASUREMENTS", "SI").upper() != "SI":
+        raise ValueError("SYSTEM_MEASUREMENTS= %s not supported (SI only)" % o["SYSTEM_MEASUREMENTS"])
+    if "REF_ELEM_LENGTH" in o:
+        raise ValueError("REF_ELEM_LENGTH is not an option of the reference (v8.4: RefElemLength is fixed to 1.0)")
+    return 1.0
+
+
 def flow_config_from_cfg(opts, nDim):
     """Values of su2b200_flow_config (keyword dict for FlowSolver.configure) from parsed cfg options."""
     o = dict(_DEFAULTS)
@@ -151,7 +159,10 @@ def flow_config_from_cfg(opts, nDim):
         nu_tilde_inf=nu_tilde, eddy_visc_inf=eddy,
         conv_scheme=capi.CONV_JST if conv == "JST" else capi.CONV_ROE,
         muscl=muscl, muscl_kappa=float(o["MUSCL_KAPPA_FLOW"]), limiter=lim,
-        venkat_coeff=float(o["VENKAT_LIMITER_COEFF"]), ref_elem_length=1.0, grad_method=gm, grad_method_recon=gr,
+        venkat_coeff=float(o["VENKAT_LIMITER_COEFF"]),
+        # this version of the reference has no REF_ELEM_LENGTH option any more: CConfig::SetPostprocessing sets
+        # RefElemLength = 1.0 (CConfig.cpp:5061; /0.3048 under SYSTEM_MEASUREMENTS= US, which this front end rejects)
+        ref_elem_length=_ref_elem_length(o), grad_method=gm, grad_method_recon=gr,
         roe_kappa=float(o["ROE_KAPPA"]), entropy_fix=float(o["ENTROPY_FIX_COEFF"]), jst_kappa2=jst[0], jst_kappa4=jst[1],
         cent_jac_fix_factor=float(o["CENTRAL_JACOBIAN_FIX_FACTOR"]), cfl=float(o["CFL_NUMBER"]),
         cfl_turb_ratio=float(o["CFL_REDUCTION_TURB"]), max_delta_time=float(o["MAX_DELTA_TIME"]),

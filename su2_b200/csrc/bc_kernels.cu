@@ -231,6 +231,7 @@ __global__ void k_bc_heatflux_wall(int nV, int Pd, double wall_heat_flux, const 
 }
 
 void flow_bc_far_field(su2b200_ctx* c, int iMarker) {
+  ++c->sys[0].A_gen;
   ProfScope prof_(c, PROF_BC);
   auto& g = c->geo;
   auto& s = c->fs;
@@ -261,6 +262,7 @@ void flow_bc_far_field(su2b200_ctx* c, int iMarker) {
 }
 
 void flow_bc_sym_plane(su2b200_ctx* c, int iMarker) {
+  ++c->sys[0].A_gen;
   ProfScope prof_(c, PROF_BC);
   auto& g = c->geo;
   auto& s = c->fs;
@@ -274,6 +276,7 @@ void flow_bc_sym_plane(su2b200_ctx* c, int iMarker) {
 }
 
 void flow_bc_heatflux_wall(su2b200_ctx* c, int iMarker) {
+  ++c->sys[0].A_gen;
   ProfScope prof_(c, PROF_BC);
   auto& g = c->geo;
   auto& s = c->fs;

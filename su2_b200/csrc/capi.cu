@@ -452,6 +452,7 @@ int su2b200_array_download(su2b200_ctx* c, int which, double* host) {
   if (which == SU2B200_ARR_ILU && c->sys[0].ilu_slim) {
     // slim factors (precond_factor.cu): the upper blocks were never copied out of the Jacobian
     const LinSys& ls = c->sys[0];
+    SU2B_REQUIRE(ls.ilu_gen == ls.A_gen, "ILU factors are stale: the Jacobian changed after the preconditioner was built");
     const size_t bs = (size_t)ls.nVar * ls.nVar;
     std::vector<double> a = ls.A.to_host();
     for (int i = 0; i < ls.Pd; ++i)
@@ -469,6 +470,25 @@ int su2b200_array_upload(su2b200_ctx* c, int which, const double* host) {
   SU2B_REQUIRE(host, "null host buffer");
   SU2B_CUDA(cudaStreamSynchronize(c->stream));
   if (n) SU2B_CUDA(cudaMemcpy(p, host, n * sizeof(double), cudaMemcpyHostToDevice));
+  if (which == SU2B200_ARR_JACOBIAN) ++c->sys[0].A_gen;
+  if (which == SU2B200_ARR_TURB_JACOBIAN) ++c->sys[1].A_gen;
+  API_END
+}
+// CSolver::InitiateComms + CompleteComms (CSolver.cpp:1406-1697) for one named per-point array: the values of the points
+// in Local_Point_P2PSend go to the neighbour ranks and land in their Local_Point_P2PRecv points (count per point =
+// array size / nPoint, the reference's COUNT_PER_POINT of CSolver.cpp:1324-1385). A single rank has nothing to exchange.
+int su2b200_halo_exchange(su2b200_ctx* c, int which) {
+  API_BEGIN
+  require_ctx(c);
+  double* p;
+  size_t n;
+  SU2B_REQUIRE(locate_array(c, which, &p, &n), "unknown array id");
+  SU2B_REQUIRE(c->geo.uploaded && c->geo.P > 0 && n % (size_t)c->geo.P == 0 && n > 0,
+               "halo exchange needs a per-point array ([nPoint][count])");
+  SU2B_REQUIRE(which != SU2B200_ARR_JACOBIAN && which != SU2B200_ARR_TURB_JACOBIAN && which != SU2B200_ARR_ILU &&
+                   which != SU2B200_ARR_INVM, "matrices are not exchanged");
+  halo_exchange(c, p, (int)(n / (size_t)c->geo.P));
+  SU2B_CUDA(cudaStreamSynchronize(c->stream));
   API_END
 }
 int su2b200_edge_counter_download(su2b200_ctx* c, signed char* host) {

@@ -54,6 +54,7 @@ static void flow_preprocessing(su2b200_ctx* c, bool output, unsigned long* nonph
   if (!output) {
     s.res.zero(c->stream);
     c->sys[0].A.zero(c->stream);
+    ++c->sys[0].A_gen;
   }
   if (!cfg.viscous) {
     if (!output && muscl && !center) {
@@ -355,6 +356,7 @@ int su2b200_linsys_set_partitions(su2b200_ctx* c, int which, int nparts) {
   auto& ls = get_sys(c, which);
   ls.nparts = std::max(1, nparts);
   ls.h_parts.clear();
+  ls.parts_explicit = false;
   API_END
 }
 
@@ -366,11 +368,49 @@ int su2b200_linsys_set_schedule(su2b200_ctx* c, int which, int apply_mode, int b
   API_END
 }
 
+int su2b200_linsys_set_wide_threshold(su2b200_ctx* c, int which, int sweep_rows, int factor_rows, int factor_mode) {
+  API_BEGIN
+  auto& ls = get_sys(c, which);
+  SU2B_CUDA(cudaStreamSynchronize(c->stream));
+  if (sweep_rows > 0 && sweep_rows != ls.wide_sweep) {
+    ls.wide_sweep = sweep_rows;
+    ls.sweep_meta_lower.release();  // build_meta() regenerates the hybrid split
+    ls.sweep_meta_upper.release();
+    ls.sweep_metar_lower.release();
+    ls.sweep_metar_upper.release();
+  }
+  if ((factor_rows > 0 && factor_rows != ls.wide_factor) || (factor_mode >= 0 && factor_mode != ls.factor_rows_mode)) {
+    if (factor_rows > 0) ls.wide_factor = factor_rows;
+    if (factor_mode >= 0) { SU2B_REQUIRE(factor_mode <= 2, "factor_mode: 0 warp per row, 1 hybrid, 2 rows kernel"); ls.factor_rows_mode = factor_mode; }
+    ls.factor_ready = false;  // factor_symbolic() regenerates descriptors and split
+  }
+  API_END
+}
+
+int su2b200_linsys_set_partition_rows(su2b200_ctx* c, int which, int nparts, const unsigned long* first_row) {
+  API_BEGIN
+  auto& ls = get_sys(c, which);
+  SU2B_REQUIRE(nparts >= 1 && first_row, "need nparts >= 1 and nparts+1 row offsets");
+  SU2B_REQUIRE(first_row[0] == 0 && (long)first_row[nparts] == ls.Pd, "partition offsets must span [0, nPointDomain]");
+  std::vector<int> h(nparts + 1);
+  for (int k = 0; k <= nparts; ++k) {
+    h[k] = (int)first_row[k];
+    if (k) SU2B_REQUIRE(h[k] >= h[k - 1], "partition offsets must ascend");
+  }
+  SU2B_CUDA(cudaStreamSynchronize(c->stream));
+  ls.nparts = nparts;
+  ls.h_parts = h;
+  ls.parts.release();
+  ls.parts_explicit = true;
+  API_END
+}
+
 int su2b200_linsys_set_matrix(su2b200_ctx* c, int which, const double* blocks) {
   API_BEGIN
   auto& ls = get_sys(c, which);
   SU2B_REQUIRE(blocks, "null matrix");
   SU2B_CUDA(cudaMemcpyAsync(ls.A.p, blocks, ls.A.n * sizeof(double), cudaMemcpyHostToDevice, c->stream));
+  ++ls.A_gen;
   SU2B_CUDA(cudaStreamSynchronize(c->stream));
   API_END
 }

@@ -150,15 +150,4 @@ int su2b200_comm_init(su2b200_ctx* c, int rank, int size, const unsigned char id
     return 0;
   } catch (const std::exception& e) { set_error(e.what()); return 1; }
 }
-int su2b200_halo_exchange(su2b200_ctx* c, int which) {
-  try {
-    if (!c) throw Error("null context");
-    double* p = nullptr;
-    size_t n = 0;
-    long sz = su2b200_array_size(c, which);
-    if (sz < 0) throw Error("unknown array id");
-    (void)p; (void)n;
-    throw Error("su2b200_halo_exchange: use the solver entry points (exchange happens inside them)");
-  } catch (const std::exception& e) { set_error(e.what()); return 1; }
-}
 }

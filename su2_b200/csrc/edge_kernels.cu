@@ -553,6 +553,7 @@ static void launch_edge(su2b200_ctx* c, const EdgeArgs& a, const FlowParams& p, 
 }
 
 void flow_edge_residual(su2b200_ctx* c, unsigned long* nonphysical_edges) {
+  ++c->sys[0].A_gen;
   auto& g = c->geo;
   auto& s = c->fs;
   auto& ls = c->sys[0];
@@ -621,6 +622,16 @@ void bench_edge_kernel(su2b200_ctx* c, int reps, float* ms_avg) {
   a.nnbr = g.nnbr.p; a.flux = s.edge_flux.p; a.A = ls.A.p; a.eij = g.edge_ij.p; a.eji = g.edge_ji.p;
   a.res = s.res.p; a.dia_ptr = g.dia_ptr.p; a.nonphys = s.counters.p + 1;
   const FlowParams p = make_flow_params(c->cfg);
+  // the kernel decrements the per-edge non-physical counters (NonPhysicalEdgeCounter is solver state) and bumps the
+  // device counter: a benchmark must leave both as it found them. The off-diagonal blocks and the edge fluxes it
+  // rewrites are scratch of the next assembly (the Jacobian is zeroed by the next Preprocessing); A_gen records it.
+  dvec<signed char> saved;
+  saved.alloc(s.edge_counter.n);
+  if (saved.n) SU2B_CUDA(cudaMemcpyAsync(saved.p, s.edge_counter.p, saved.n, cudaMemcpyDeviceToDevice, c->stream));
+  unsigned long long cnt[2] = {0, 0};
+  SU2B_CUDA(cudaMemcpyAsync(cnt, s.counters.p, sizeof(cnt), cudaMemcpyDeviceToHost, c->stream));
+  SU2B_CUDA(cudaStreamSynchronize(c->stream));
+  ++ls.A_gen;
   SU2B_CUDA(cudaEventRecord(c->ev0, c->stream));
   for (int r = 0; r < reps; ++r) {
     if (g.nDim == 2) launch_edge<2>(c, a, p, g.E, false); else launch_edge<3>(c, a, p, g.E, false);
@@ -630,6 +641,9 @@ void bench_edge_kernel(su2b200_ctx* c, int reps, float* ms_avg) {
   float ms = 0;
   SU2B_CUDA(cudaEventElapsedTime(&ms, c->ev0, c->ev1));
   *ms_avg = ms / reps;
+  if (saved.n) SU2B_CUDA(cudaMemcpyAsync(s.edge_counter.p, saved.p, saved.n, cudaMemcpyDeviceToDevice, c->stream));
+  SU2B_CUDA(cudaMemcpyAsync(s.counters.p, cnt, sizeof(cnt), cudaMemcpyHostToDevice, c->stream));
+  SU2B_CUDA(cudaStreamSynchronize(c->stream));
 }
 
 }  // namespace su2b200

@@ -919,6 +919,7 @@ void flow_vorticity_strain(su2b200_ctx* c) {
 template <int NV>
 static void prepare_implicit_impl(su2b200_ctx* c, LinSys& ls, const double* dt, double* res, double* sol,
                                   double* out_rms, double* out_max, unsigned long* out_idx) {
+  ++ls.A_gen;  // V/dt lands on the diagonal blocks
   auto& g = c->geo;
   auto& s = c->fs;
   const int nb = nblk(g.Pd, 256);

@@ -144,6 +144,12 @@ struct LinSys {
   int sweep_mode = 2;                // apply: 2 data-polling sweeps (precond_poll.cu), 1 flag sweeps, 0 launch per level
   int build_mode = 2;                // factor: 2 single-launch polling factorisation (precond_factor.cu), 1 flag sweep,
                                      //         0 launch per level
+  int wide_sweep = 4096, wide_factor = 4096;  // level width from which the nVar-lanes-per-row kernels take over
+  int factor_rows_mode = 1;                   // 0 warp-per-row only, 1 hybrid, 2 rows kernel only (k_factor_rows)
+  bool parts_explicit = false;                // h_parts given by su2b200_linsys_set_partition_rows
+  // generation of the matrix values (bumped by every writer of A) and the one the ILU factors were built from: the
+  // slim factors read the upper blocks from A at apply time, so an apply after A changed must fail loudly
+  unsigned long A_gen = 1, ilu_gen = 0;
   bool factor_ready = false, factor_ok = false;
   dvec<int> factor_desc, factor_ops;  // symbolic factorisation: row descriptors (level order) and update lists
   int factor_own_cap = 0, factor_src_cap = 0;

@@ -164,6 +164,9 @@ __global__ void k_mgs_logic(double* __restrict__ sc, int mode, int k) {
     const double nrm = sqrt(prod);
     sc[5] = nrm;
     sc[8 + k] = nrm;
+    // a NaN here (a poisoned basis, e.g. the sentinel of a sweep whose watchdog fired) must stop the solve now: the
+    // reference would only notice at the start of the next orthogonalisation, after scaling the vector by it
+    if (prod != prod) sc[4] = 1.0;
   }
 }
 __global__ void k_div_dev(size_t n, const double* __restrict__ sc, double* __restrict__ x) {
@@ -333,6 +336,7 @@ unsigned long linsys_solve(su2b200_ctx* c, LinSys& ls, int solver, int prec, dou
   linsys_build_prec(c, ls, prec);
   unsigned long it = 0;
   double res = 0.0;
+  try {
   switch (solver) {
     case SU2B200_SOLVER_FGMRES:
       it = fgmres(c, ls, prec, tol, max_iter, b, x, true, &res);
@@ -355,6 +359,12 @@ unsigned long linsys_solve(su2b200_ctx* c, LinSys& ls, int solver, int prec, dou
       break;
     default:
       throw Error("unknown linear solver");
+  }
+  } catch (...) {
+    // a fired sweep watchdog is the root cause of whatever failed downstream (NaN norms): report THAT, and clear the
+    // abort flag so that the next build/apply on this system does not stop at once
+    linsys_check_sweeps(c, ls);
+    throw;
   }
   linsys_check_sweeps(c, ls);
   if (residual) *residual = res;

@@ -674,7 +674,10 @@ void linsys_check_sweeps(su2b200_ctx* c, LinSys& ls) {
 
 // nnz-balanced partitions, CSysMatrix::Initialize (CSysMatrix.cpp:199-227)
 static void build_partitions(LinSys& ls, int nparts) {
-  if ((int)ls.h_parts.size() == nparts + 1) return;
+  if ((int)ls.h_parts.size() == nparts + 1) {
+    if (ls.parts.n != ls.h_parts.size()) ls.parts.upload(ls.h_parts);  // explicit boundaries (set_partition_rows)
+    return;
+  }
   const auto& rp = ls.h_row_ptr;
   const int n = ls.Pd;
   ls.h_parts.assign(nparts + 1, n);
@@ -695,6 +698,7 @@ static void ilu_build_impl(su2b200_ctx* c, LinSys& ls) {
   ls.invM.alloc((size_t)ls.Pd * NV * NV);
   if (ls.nparts <= 1) build_levels(ls);
   ls.ilu_slim = false;
+  ls.ilu_gen = ls.A_gen;
   if (ls.nparts <= 1 && ls.build_mode == 2 && factor_symbolic(ls)) {
     ilu_factor_poll(c, ls);  // reads A, writes ILU: no copy
     return;

@@ -724,7 +724,7 @@ bool factor_symbolic(LinSys& ls) {
       empty.b = make_int4(0, 0, 0, 0);
       // wide middle (first to last level of at least `wide` rows): k_factor_rows; the narrow head and tail, where the
       // latency of a level counts and not the rows in it, stay with the warp-per-row kernel
-      static const int wide = getenv("SU2B200_FACTOR_WIDE") ? atoi(getenv("SU2B200_FACTOR_WIDE")) : 4096;
+      const int wide = getenv("SU2B200_FACTOR_WIDE") ? atoi(getenv("SU2B200_FACTOR_WIDE")) : ls.wide_factor;
       int first = -1, last = -1;
       const int nLev = (int)ls.lvl_ptr_lower.size() - 1;
       for (int l = 0; l < nLev; ++l)
@@ -854,7 +854,7 @@ static void factor_launch_rows(su2b200_ctx* c, LinSys& ls, int gbeg, int gend) {
 // (warp per row) for everything, =2: k_factor_rows for everything.
 template <int NV>
 static void factor_block(su2b200_ctx* c, LinSys& ls) {
-  static const int rows = getenv("SU2B200_FACTOR_ROWS") ? atoi(getenv("SU2B200_FACTOR_ROWS")) : 1;
+  const int rows = getenv("SU2B200_FACTOR_ROWS") ? atoi(getenv("SU2B200_FACTOR_ROWS")) : ls.factor_rows_mode;
   // slim ILU: when no upper block changes (7-point hexahedral stencils: every update lands on a diagonal) and the
   // polling sweeps are the consumer, the upper blocks stay in the Jacobian: not read, not written here
   static const int slimOk = getenv("SU2B200_ILU_SLIM") ? atoi(getenv("SU2B200_ILU_SLIM")) : 1;

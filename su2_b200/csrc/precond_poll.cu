@@ -565,7 +565,7 @@ static void build_meta(LinSys& ls) {
     // hybrid schedule: the contiguous run of wide levels [first, last] goes to the rows kernel, the narrow head and tail
     // to the warp-per-row kernel. split = {rows before the run, groups before the run, rows at its end, groups at its end}
     // (185^3, ms per application: threshold 1024 -> 3.75, 4096 -> 3.53, 16384 -> 3.46; warp-per-row only 3.97)
-    const int wide = getenv("SU2B200_SWEEP_WIDE") ? atoi(getenv("SU2B200_SWEEP_WIDE")) : 4096;
+    const int wide = getenv("SU2B200_SWEEP_WIDE") ? atoi(getenv("SU2B200_SWEEP_WIDE")) : ls.wide_sweep;
     auto split = [&](const std::vector<int>& ptr, int (&sp)[4]) {
       const int nl = (int)ptr.size() - 1;
       int first = -1, last = -1;
@@ -640,6 +640,9 @@ static void ilu_apply_poll_impl(su2b200_ctx* c, LinSys& ls, const double* x, dou
 }
 
 void ilu_apply_poll(su2b200_ctx* c, LinSys& ls, const double* x, double* y) {
+  // slim factors keep U in the Jacobian: L, D and invM of one matrix must not be combined with the U of another
+  SU2B_REQUIRE(!(ls.ilu_slim && ls.ilu_gen != ls.A_gen),
+               "ILU preconditioner is stale: the matrix changed after BuildILUPreconditioner (rebuild before applying)");
   const size_t n = ls.vecLen();
   if (ls.sweep_tmp.n != n) { ls.sweep_tmp.alloc(n); ls.sweep_tmp.zero(c->stream); }
   if (ls.sweep_tmp2.n != n && x == y) { ls.sweep_tmp2.alloc(n); ls.sweep_tmp2.zero(c->stream); }

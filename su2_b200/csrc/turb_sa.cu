@@ -320,6 +320,7 @@ void turb_set_time_step(su2b200_ctx* c) {
 }
 
 void turb_space_integration(su2b200_ctx* c) {
+  ++c->sys[1].A_gen;
   auto& g = c->geo;
   auto& s = c->fs;
   auto& ls = c->sys[1];

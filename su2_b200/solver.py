@@ -150,6 +150,19 @@ class FlowSolver:
         assert uid.size == 128
         check(self.lib.su2b200_comm_init(self.ctx, int(rank), int(size), uid.ctypes.data_as(C.POINTER(C.c_ubyte))))
 
+    def halo_exchange(self, name):
+        """InitiateComms/CompleteComms of a named per-point array (su2b200_halo_exchange)."""
+        check(self.lib.su2b200_halo_exchange(self.ctx, capi.ARR[name]))
+
+    def set_partition_rows(self, which, first_row):
+        """Explicit block-Jacobi partitions of system `which` (su2b200_linsys_set_partition_rows)."""
+        fr = as_ulong(first_row)
+        check(self.lib.su2b200_linsys_set_partition_rows(self.ctx, int(which), len(fr) - 1, ptr_ul(fr)))
+
+    def set_wide_threshold(self, which, sweep_rows=0, factor_rows=0, factor_mode=-1):
+        check(self.lib.su2b200_linsys_set_wide_threshold(self.ctx, int(which), int(sweep_rows), int(factor_rows),
+                                                         int(factor_mode)))
+
     def edge_counter(self):
         out = np.empty(self.nEdge, dtype=np.int8)
         check(self.lib.su2b200_edge_counter_download(self.ctx, out.ctypes.data_as(C.POINTER(C.c_byte))))
@@ -322,6 +335,15 @@ class LinearSystem:
     def set_schedule(self, apply_mode=-1, build_mode=-1):
         """ILU0 kernel schedules (see su2b200_linsys_set_schedule); -1 keeps the current one."""
         check(self.lib.su2b200_linsys_set_schedule(self.ctx, self.which, int(apply_mode), int(build_mode)))
+
+    def set_wide_threshold(self, sweep_rows=0, factor_rows=0, factor_mode=-1):
+        """Level width from which the nVar-lanes-per-row ILU kernels take over (su2b200_linsys_set_wide_threshold)."""
+        check(self.lib.su2b200_linsys_set_wide_threshold(self.ctx, self.which, int(sweep_rows), int(factor_rows),
+                                                         int(factor_mode)))
+
+    def set_partition_rows(self, first_row):
+        fr = as_ulong(first_row)
+        check(self.lib.su2b200_linsys_set_partition_rows(self.ctx, self.which, len(fr) - 1, ptr_ul(fr)))
 
     def set_matrix(self, blocks):
         b = as_f64(blocks).ravel()

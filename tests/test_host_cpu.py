@@ -14,7 +14,8 @@ from su2_b200.config import parse_cfg, flow_config_from_cfg, mesh_from_cfg
 from su2_b200.mesh import Mesh
 
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
-CASES = ["naca0012_roe", "naca0012_jst", "box_euler", "rect_ns", "box_rans_sa"]
+CASES = ["naca0012_roe", "naca0012_jst", "box_euler", "rect_ns", "box_rans_sa", "rect_rans_sa", "naca0012_jacobi",
+         "naca0012_fgmres_lusgs", "naca0012_bcgstab_ilu", "naca0012_rfgmres", "naca0012_ls"]
 GENERATED = ["box_euler", "rect_ns", "box_rans_sa"]
 
 
@@ -61,7 +62,7 @@ def test_cfg_front_end_matches_reference_config(case):
     ref = config_from_dump(gold)
     opts = parse_cfg(open(os.path.join(ROOT, "tests", "cases", case + ".cfg")).read())
     got = flow_config_from_cfg(opts, int(gold["nDim"]))
-    skip = {"turb_linear_solver", "turb_linear_prec", "turb_linear_tol", "turb_linear_iter", "ref_elem_length"}
+    skip = {"turb_linear_solver", "turb_linear_prec", "turb_linear_tol", "turb_linear_iter"}
     if not ref["rans_sa"]:
         skip |= {"nu_tilde_inf", "eddy_visc_inf"}  # set by the reference whatever the solver, unused without SA
     for k, v in ref.items():
