@@ -27,7 +27,8 @@ def load_dump(path):
             a = np.frombuffer(f.read(n * dtype.itemsize), dtype=dtype).reshape(dims)
             if dt == 3:
                 out[name] = a.tobytes().decode()
-            elif a.size == 1 and nd == 1 and (name.startswith("cfg_") or name.startswith("enum_") or name in (
+            elif a.size == 1 and nd == 1 and (name.startswith("cfg_") or name.startswith("enum_") or name.split("_", 1)[-1] in (
+                    "nDim", "nPoint", "nPointDomain", "nEdge", "nMarker") or name in (
                     "nDim", "nPoint", "nPointDomain", "nEdge", "nMarker", "nIter") or name.endswith(("_kind", "_monitoring", "_heat_flux", "_iter", "_res", "_dt"))):
                 out[name] = a.reshape(()).item()
             else:

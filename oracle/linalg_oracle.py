@@ -117,6 +117,48 @@ def ilu0_apply(row_ptr, col_ind, dia_ptr, ilu, invM, x, nPointDomain=None):
     return y
 
 
+def gauss_elimination(a, v):
+    """Solve a x = v without pivoting (CSysMatrix::Gauss_Elimination, CSysMatrix.cpp:510-545): forward elimination of
+    matrix and right-hand side together, regularised pivots, back substitution."""
+    a = np.array(a, dtype=np.float64)
+    v = np.array(v, dtype=np.float64)
+    n = a.shape[0]
+    for i in range(1, n):
+        for j in range(i):
+            a[j, j] = _regularize(a[j, j])
+            w = a[i, j] / a[j, j]
+            for k in range(j, n):
+                a[i, k] -= w * a[j, k]
+            v[i] -= w * v[j]
+    for i in range(n - 1, -1, -1):
+        for j in range(i + 1, n):
+            v[i] -= a[i, j] * v[j]
+        a[i, i] = _regularize(a[i, i])
+        v[i] /= a[i, i]
+    return v
+
+
+def lusgs_apply(row_ptr, col_ind, dia_ptr, A, x, nPointDomain=None):
+    """One symmetric Gauss-Seidel sweep, single partition (ComputeLU_SGSPreconditioner, CSysMatrix.cpp:826-888):
+    (D+L) x* = b, then (D+U) x = D x*; every row solved with the diagonal block by Gauss elimination."""
+    nv = A.shape[1]
+    n = len(row_ptr) - 1 if nPointDomain is None else nPointDomain
+    b = np.array(x, dtype=np.float64).reshape(-1, nv)
+    y = np.zeros_like(b)
+    for i in range(n):
+        low = np.zeros(nv)
+        for idx in range(row_ptr[i], dia_ptr[i]):
+            low += A[idx] @ y[col_ind[idx]]
+        y[i] = gauss_elimination(A[dia_ptr[i]], b[i] - low)
+    for i in range(n - 1, -1, -1):
+        dia = A[dia_ptr[i]] @ y[i]
+        up = np.zeros(nv)
+        for idx in range(dia_ptr[i] + 1, row_ptr[i + 1]):
+            up += A[idx] @ y[col_ind[idx]]  # halo columns included (they hold the exchanged x*)
+        y[i] = gauss_elimination(A[dia_ptr[i]], dia - up)
+    return y
+
+
 def _sign(x, y):
     return -abs(x) if y < 0.0 else abs(x)
 

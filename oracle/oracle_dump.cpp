@@ -46,6 +46,7 @@
 #include "SU2_CFD/include/solvers/CNSSolver.hpp"
 #include "SU2_CFD/include/solvers/CTurbSASolver.hpp"
 #include "SU2_CFD/include/integration/CIntegration.hpp"
+#include "SU2_CFD/include/integration/CMultiGridIntegration.hpp"
 #include "SU2_CFD/include/variables/CEulerVariable.hpp"
 #include "SU2_CFD/include/variables/CNSVariable.hpp"
 #include "SU2_CFD/include/variables/CTurbSAVariable.hpp"
@@ -100,19 +101,21 @@ class Dumper : public CSinglezoneDriver {
  public:
   Dumper(char* cfg) : CSinglezoneDriver(cfg, 1, SU2_MPI::GetComm()) {}
 
-  void DumpGeometry(Writer& w) {
-    CGeometry* g = geometry_container[ZONE_0][INST_0][MESH_0];
+  void DumpGeometry(Writer& w) { DumpGeometryLevel(w, geometry_container[ZONE_0][INST_0][MESH_0], ""); }
+
+  // geometry of one (multigrid) level; names prefixed with G ("" on the finest grid, "mg<k>_" on coarse level k)
+  void DumpGeometryLevel(Writer& w, CGeometry* g, const std::string& G) {
     CConfig* cfg = config_container[ZONE_0];
     const unsigned long nDim = g->GetnDim(), P = g->GetnPoint(), Pd = g->GetnPointDomain(), E = g->GetnEdge();
-    w.iscalar("nDim", nDim); w.iscalar("nPoint", P); w.iscalar("nPointDomain", Pd); w.iscalar("nEdge", E);
+    w.iscalar(G + "nDim", nDim); w.iscalar(G + "nPoint", P); w.iscalar(G + "nPointDomain", Pd); w.iscalar(G + "nEdge", E);
     std::vector<long> en(2 * E);
     std::vector<double> nrm(E * nDim);
     for (unsigned long e = 0; e < E; ++e) {
       en[e] = g->edges->GetNode(e, 0); en[E + e] = g->edges->GetNode(e, 1);
       for (unsigned long d = 0; d < nDim; ++d) nrm[e * nDim + d] = g->edges->GetNormal(e)[d];
     }
-    w.i64("edge_nodes", {2, E}, en.data());
-    w.f64("edge_normal", {E, nDim}, nrm.data());
+    w.i64(G + "edge_nodes", {2, E}, en.data());
+    w.f64(G + "edge_normal", {E, nDim}, nrm.data());
     std::vector<double> coord(P * nDim), vol(P), wd(P);
     std::vector<long> gidx(P), nnb(P), pb(P);
     for (unsigned long i = 0; i < P; ++i) {
@@ -123,14 +126,14 @@ class Dumper : public CSinglezoneDriver {
       nnb[i] = g->nodes->GetnNeighbor(i);
       pb[i] = g->nodes->GetPhysicalBoundary(i);
     }
-    w.f64("coord", {P, nDim}, coord.data()); w.f64("volume", {P}, vol.data()); w.f64("wall_distance", {P}, wd.data());
-    w.i64("global_index", {P}, gidx.data()); w.i64("nNeighbor", {P}, nnb.data()); w.i64("physical_boundary", {P}, pb.data());
+    w.f64(G + "coord", {P, nDim}, coord.data()); w.f64(G + "volume", {P}, vol.data()); w.f64(G + "wall_distance", {P}, wd.data());
+    w.i64(G + "global_index", {P}, gidx.data()); w.i64(G + "nNeighbor", {P}, nnb.data()); w.i64(G + "physical_boundary", {P}, pb.data());
     std::vector<long> pptr(P + 1, 0), pnbr, pedge;
     for (unsigned long i = 0; i < P; ++i) {
       for (unsigned short k = 0; k < g->nodes->GetnPoint(i); ++k) { pnbr.push_back(g->nodes->GetPoint(i, k)); pedge.push_back(g->nodes->GetEdge(i, k)); }
       pptr[i + 1] = pnbr.size();
     }
-    w.i64("point_ptr", {P + 1}, pptr.data()); w.i64("point_nbr", {pnbr.size()}, pnbr.data()); w.i64("point_edge", {pedge.size()}, pedge.data());
+    w.i64(G + "point_ptr", {P + 1}, pptr.data()); w.i64(G + "point_nbr", {pnbr.size()}, pnbr.data()); w.i64(G + "point_edge", {pedge.size()}, pedge.data());
     const auto& pat = g->GetSparsePattern(ConnectivityType::FiniteVolume, 0);
     const auto& emap = g->GetEdgeToSparsePatternMap();
     const unsigned long nnz = pat.getNumNonZeros();
@@ -139,13 +142,13 @@ class Dumper : public CSinglezoneDriver {
     for (unsigned long k = 0; k < nnz; ++k) ci[k] = pat.innerIdx()[k];
     for (unsigned long i = 0; i < P; ++i) dp[i] = pat.diagPtr()[i];
     for (unsigned long e = 0; e < E; ++e) { ep[2 * e] = emap(e, 0); ep[2 * e + 1] = emap(e, 1); }
-    w.i64("row_ptr", {P + 1}, rp.data()); w.i64("col_ind", {nnz}, ci.data()); w.i64("dia_ptr", {P}, dp.data()); w.i64("edge_ptr", {E, 2}, ep.data());
+    w.i64(G + "row_ptr", {P + 1}, rp.data()); w.i64(G + "col_ind", {nnz}, ci.data()); w.i64(G + "dia_ptr", {P}, dp.data()); w.i64(G + "edge_ptr", {E, 2}, ep.data());
     // markers
     const unsigned short nM = g->GetnMarker();
-    w.iscalar("nMarker", nM);
+    w.iscalar(G + "nMarker", nM);
     for (unsigned short m = 0; m < nM; ++m) {
       const std::string tag = cfg->GetMarker_All_TagBound(m);
-      const std::string pre = "marker" + std::to_string(m) + "_";
+      const std::string pre = G + "marker" + std::to_string(m) + "_";
       w.text(pre + "tag", tag);
       w.iscalar(pre + "kind", cfg->GetMarker_All_KindBC(m));
       w.iscalar(pre + "monitoring", cfg->GetMarker_All_Monitoring(m));
@@ -252,6 +255,136 @@ class Dumper : public CSinglezoneDriver {
       const unsigned long nnz = s->Jacobian.nnz;
       w.f64(pre + "jacobian", {nnz, nVar, nVar}, s->Jacobian.matrix);
     }
+  }
+
+  // ---- FAS multigrid (MGLEVEL > 0): CMultiGridIntegration::MultiGrid_Cycle (CMultiGridIntegration.cpp:129-300) replayed
+  //      call by call through the reference's own member functions, with the state of every level written after each
+  //      transfer step of the dumped iterations ("it<i>_ev<n>_<what>_L<level>", n = running event number of the cycle)
+  int mgEvent = 0;
+  void MGDumpLevel(Writer& w, const std::string& pre, const char* what, unsigned short iMesh, bool sol, bool res, bool trunc) {
+    CGeometry* g = geometry_container[ZONE_0][INST_0][iMesh];
+    CSolver* s = solver_container[ZONE_0][INST_0][iMesh][FLOW_SOL];
+    const unsigned long P = g->GetnPoint(), nVar = s->GetnVar();
+    const std::string name = pre + "ev" + std::to_string(mgEvent++) + "_" + what + "_L" + std::to_string(iMesh);
+    if (sol) dump_matrix(w, name + "_solution", s->GetNodes()->GetSolution(), P, nVar);
+    if (res) dump_sysvec(w, name + "_linsysres", s->LinSysRes, P, nVar);
+    if (trunc) {
+      std::vector<double> t(P * nVar);
+      for (unsigned long i = 0; i < P; ++i) for (unsigned long v = 0; v < nVar; ++v) t[i * nVar + v] = s->GetNodes()->GetResTruncError(i)[v];
+      w.f64(name + "_trunc", {P, nVar}, t.data());
+    }
+  }
+  void MGCycle(Writer& w, bool D, const std::string& pre, unsigned short iMesh, unsigned short RecursiveParam) {
+    CConfig* config = config_container[ZONE_0];
+    auto* mg = static_cast<CMultiGridIntegration*>(integration_container[ZONE_0][INST_0][FLOW_SOL]);
+    CGeometry* gf = geometry_container[ZONE_0][INST_0][iMesh];
+    CSolver** scf = solver_container[ZONE_0][INST_0][iMesh];
+    CSolver* sf = scf[FLOW_SOL];
+    CNumerics** nf = numerics_container[ZONE_0][INST_0][iMesh][FLOW_SOL];
+    auto smooth = [&](unsigned short n) {
+      for (unsigned short k = 0; k < n; ++k) {
+        sf->Preprocessing(gf, scf, config, iMesh, 0, RUNTIME_FLOW_SYS, false);
+        sf->Set_OldSolution();
+        sf->SetTime_Step(gf, scf, config, iMesh, config->GetTimeIter());
+        mg->Space_Integration(gf, scf, nf, config, iMesh, 0, RUNTIME_FLOW_SYS);
+        mg->Time_Integration(gf, scf, config, 0, RUNTIME_FLOW_SYS);
+        sf->Postprocessing(gf, scf, config, iMesh);
+      }
+    };
+    smooth(config->GetMG_PreSmooth(iMesh));
+    if (D) MGDumpLevel(w, pre, "presmooth", iMesh, true, false, false);
+    if (iMesh < config->GetnMGLevels()) {
+      CGeometry* gc = geometry_container[ZONE_0][INST_0][iMesh + 1];
+      CSolver** scc = solver_container[ZONE_0][INST_0][iMesh + 1];
+      CSolver* sc = scc[FLOW_SOL];
+      CNumerics** nc = numerics_container[ZONE_0][INST_0][iMesh + 1][FLOW_SOL];
+      config->SetKind_TimeIntScheme(EULER_EXPLICIT);
+      sf->Preprocessing(gf, scf, config, iMesh, NO_RK_ITER, RUNTIME_FLOW_SYS, false);
+      mg->Space_Integration(gf, scf, nf, config, iMesh, NO_RK_ITER, RUNTIME_FLOW_SYS);
+      mg->SetResidual_Term(gf, sf);
+      if (D) MGDumpLevel(w, pre, "fineres", iMesh, false, true, false);
+      mg->SetRestricted_Solution(RUNTIME_FLOW_SYS, sf, sc, gf, gc, config);
+      sc->Preprocessing(gc, scc, config, iMesh + 1, NO_RK_ITER, RUNTIME_FLOW_SYS, false);
+      mg->Space_Integration(gc, scc, nc, config, iMesh + 1, NO_RK_ITER, RUNTIME_FLOW_SYS);
+      if (D) MGDumpLevel(w, pre, "coarseres", iMesh + 1, true, true, false);
+      mg->SetForcing_Term(sf, sc, gf, gc, config, iMesh + 1);
+      if (D) MGDumpLevel(w, pre, "forcing", iMesh + 1, false, false, true);
+      config->SetKind_TimeIntScheme(EULER_IMPLICIT);
+      for (unsigned short imu = 0; imu <= RecursiveParam; imu++) {
+        unsigned short next = RecursiveParam;
+        if (iMesh == config->GetnMGLevels() - 2) next = 0;
+        MGCycle(w, D, pre, iMesh + 1, next);
+      }
+      mg->GetProlongated_Correction(RUNTIME_FLOW_SYS, sf, sc, gf, gc, config);
+      mg->SmoothProlongated_Correction(RUNTIME_FLOW_SYS, sf, gf, config->GetMG_CorrecSmooth(iMesh), 1.25, config);
+      if (D) MGDumpLevel(w, pre, "correction", iMesh, false, true, false);
+      mg->SetProlongated_Correction(sf, gf, config, iMesh);
+      if (D) MGDumpLevel(w, pre, "corrected", iMesh, true, false, false);
+      smooth(config->GetMG_PostSmooth(iMesh));
+    }
+  }
+  void RunMG(const char* out, int nIter, const std::set<int>& dumpIters) {
+    Writer w(out);
+    CConfig* config = config_container[ZONE_0];
+    CGeometry* g = geometry_container[ZONE_0][INST_0][MESH_0];
+    CSolver** solvers = solver_container[ZONE_0][INST_0][MESH_0];
+    auto* flow = static_cast<CEulerSolver*>(solvers[FLOW_SOL]);
+    auto* mg = static_cast<CMultiGridIntegration*>(integration_container[ZONE_0][INST_0][FLOW_SOL]);
+    const unsigned long nVar = flow->nVar;
+    const unsigned short nLev = config->GetnMGLevels();
+    Preprocess(0);
+    DumpGeometry(w);
+    DumpConfig(w);
+    w.iscalar("nIter", nIter);
+    w.iscalar("cfg_mg_levels", nLev);
+    w.iscalar("cfg_mg_cycle", config->GetMGCycle());
+    w.scalar("cfg_mg_damp_restriction", config->GetDamp_Res_Restric());
+    w.scalar("cfg_mg_damp_prolongation", config->GetDamp_Correc_Prolong());
+    w.scalar("cfg_lax_kappa1", config->GetKappa_1st_Flow());
+    std::vector<long> pre(nLev + 1), post(nLev + 1), corr(nLev + 1);
+    std::vector<double> cfl(nLev + 1);
+    for (unsigned short l = 0; l <= nLev; ++l) { pre[l] = config->GetMG_PreSmooth(l); post[l] = config->GetMG_PostSmooth(l); corr[l] = config->GetMG_CorrecSmooth(l); cfl[l] = config->GetCFL(l); }
+    w.i64("cfg_mg_pre_smooth", {(unsigned long)nLev + 1}, pre.data()); w.i64("cfg_mg_post_smooth", {(unsigned long)nLev + 1}, post.data());
+    w.i64("cfg_mg_correction_smooth", {(unsigned long)nLev + 1}, corr.data()); w.f64("cfg_mg_cfl", {(unsigned long)nLev + 1}, cfl.data());
+    for (unsigned short l = 1; l <= nLev; ++l) {
+      CGeometry* gc = geometry_container[ZONE_0][INST_0][l];
+      const std::string G = "mg" + std::to_string(l) + "_";
+      DumpGeometryLevel(w, gc, G);
+      // agglomeration: children (points of level l-1) of every coarse point, CSR
+      const unsigned long Pc = gc->GetnPoint();
+      std::vector<long> cptr(Pc + 1, 0), child;
+      for (unsigned long i = 0; i < Pc; ++i) {
+        for (unsigned short k = 0; k < gc->nodes->GetnChildren_CV(i); ++k) child.push_back(gc->nodes->GetChildren_CV(i, k));
+        cptr[i + 1] = child.size();
+      }
+      w.i64(G + "children_ptr", {Pc + 1}, cptr.data()); w.i64(G + "children", {child.size()}, child.data());
+    }
+    std::vector<double> hist;
+    for (int it = 0; it < nIter; ++it) {
+      config->SetInnerIter(it);
+      const bool D = dumpIters.count(it) > 0;
+      const std::string p = "it" + std::to_string(it) + "_";
+      config->SetGlobalParam(config->GetKind_Solver(), RUNTIME_FLOW_SYS);
+      if (D) dump_matrix(w, p + "pre_solution", flow->nodes->GetSolution(), g->GetnPoint(), nVar);
+      mgEvent = 0;
+      unsigned short rec = config->GetMGCycle();
+      if (rec == FULLMG_CYCLE) rec = V_CYCLE;
+      MGCycle(w, D, p, MESH_0, rec);
+      flow->Preprocessing(g, solvers, config, MESH_0, NO_RK_ITER, RUNTIME_FLOW_SYS, true);
+      flow->Pressure_Forces(g, config);
+      flow->Momentum_Forces(g, config);
+      flow->Friction_Forces(g, config);
+      if (D) dump_matrix(w, p + "post_solution", flow->nodes->GetSolution(), g->GetnPoint(), nVar);
+      for (unsigned v = 0; v < 5; ++v) hist.push_back(v < nVar ? flow->GetRes_RMS(v) : 0.0);
+      hist.push_back(0.0);
+      hist.push_back(flow->GetTotal_CL()); hist.push_back(flow->GetTotal_CD());
+      hist.push_back((double)flow->GetIterLinSolver()); hist.push_back(flow->GetResLinSolver());
+      hist.push_back(0.0); hist.push_back(0.0);
+      fprintf(stderr, "[oracle_dump mg] it %d rms0 %.9e CL %.9f CD %.9f linit %lu\n", it, flow->GetRes_RMS(0), flow->GetTotal_CL(), flow->GetTotal_CD(), flow->GetIterLinSolver());
+    }
+    (void)mg;
+    w.f64("history", {(unsigned long)nIter, 12}, hist.data());
+    dump_matrix(w, "final_solution", flow->nodes->GetSolution(), g->GetnPoint(), nVar);
   }
 
   void Run(const char* out, int nIter, const std::set<int>& dumpIters) {
@@ -418,7 +551,8 @@ int main(int argc, char** argv) {
     std::ofstream devnull("/dev/null");
     if (!getenv("ORACLE_DUMP_VERBOSE")) std::cout.rdbuf(devnull.rdbuf());
     Dumper d(argv[1]);
-    d.Run(argv[2], nIter, dumpIters);
+    if (d.config_container[ZONE_0]->GetnMGLevels() > 0) d.RunMG(argv[2], nIter, dumpIters);
+    else d.Run(argv[2], nIter, dumpIters);
     std::cout.rdbuf(orig);
   }
   return 0;

@@ -314,6 +314,9 @@ __global__ void __launch_bounds__(128) k_poll_sweep_pipe(int n, const int4* __re
 #ifndef ROWS_CH
 #define ROWS_CH 3
 #endif
+#ifndef ROWS_U
+#define ROWS_U 2  // row groups per warp and iteration of the wide-level kernel (k_poll_sweep_rowsU); levels are padded to it
+#endif
 #ifndef ROWS_MIN_BLOCKS
 #define ROWS_MIN_BLOCKS 5
 #endif
@@ -406,6 +409,147 @@ __global__ void __launch_bounds__(128, ROWS_MIN_BLOCKS) k_poll_sweep_rows(int nG
       if (on && ok) st_relaxed(out + (size_t)i * NV + r, x);
     }
     ok = __all_sync(FULLM, ok);
+  }
+}
+
+// ---- the same mapping, U row groups per warp and iteration -----------------------------------------------------------------
+// What bounds the wide levels (measured, 185^3, RCM order; profiles/r02_ilu_apply_ab.txt): the sweep is a chain of 553
+// levels per direction, and a level of n rows takes ceil(n / R) consumer iterations of ~1.2 us each, R = rows in flight
+// = SMs * resident warps * rows per warp. Six variants with 8..20 resident warps per SM all fall on
+//     t = 1.96 ms + 16.8 ms / (warps per SM)        [= 2 tau (L + N / R), tau = 1.18 us, L = 553 levels, N = 6.33 M rows],
+// whether the factor entries come through registers or through a cp.async ring two or three groups deep (the ring
+// variants were slower only because their shared memory left 12-16 warps resident instead of 20), and looking at the
+// next group's dependencies one iteration early changed nothing (a warp's next group sits a whole wave further on,
+// i.e. mostly in the NEXT level, whose dependencies are still being produced). So the lever is R: with U = 2 groups of
+// the same level per iteration, handled as one interleaved instruction stream, 16 warps * 12 rows * 148 SMs = 28 k rows
+// are in flight -- more than the widest level (25.6 k) -- and every level costs ONE round trip. Levels are padded to
+// U * 32/nVar rows, so the groups of an iteration never depend on one another. Descriptors run two iterations ahead
+// and columns one iteration ahead in registers, which also takes the descriptor -> columns part off the latency chain
+// of an iteration. Same arithmetic in the same order as k_poll_sweep_rows: bit-identical results.
+#ifndef ROWSU_MIN_BLOCKS
+#define ROWSU_MIN_BLOCKS 4
+#endif
+template <int NV, bool FORWARD, int U>
+__global__ void __launch_bounds__(128, ROWSU_MIN_BLOCKS) k_poll_sweep_rowsU(int nIters, const int4* __restrict__ meta, int* ctrl,
+                                                          const int* __restrict__ col_ind, const double* __restrict__ ILU,
+                                                          const double* __restrict__ invM, const double* __restrict__ in,
+                                                          double* out) {
+  constexpr int LPB = NV * NV, RPW = 32 / NV, CH = ROWS_CH;
+  const int lane = threadIdx.x & 31;
+  const int sub = lane / NV, r = lane % NV;
+  const bool live = sub < RPW;
+  const int W = gridDim.x * (blockDim.x >> 5);
+  const int q0 = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
+  if (q0 >= nIters) return;
+  auto load_meta = [&](int q, int u) {
+    return (live && q < nIters) ? meta[((size_t)q * U + u) * RPW + sub] : make_int4(-1, 0, 0, 0);
+  };
+  int4 m0[U], m1[U];  // descriptors of iteration q and q+W
+  int jj[U][CH];      // columns of iteration q
+#pragma unroll
+  for (int u = 0; u < U; ++u) {
+    m0[u] = load_meta(q0, u);
+    m1[u] = load_meta(q0 + W, u);
+  }
+#pragma unroll
+  for (int u = 0; u < U; ++u)
+#pragma unroll
+    for (int k = 0; k < CH; ++k) jj[u][k] = (m0[u].x >= 0 && m0[u].y + k < m0[u].z) ? col_ind[m0[u].y + k] : 0;
+  bool ok = true;  // after the watchdog fired the lanes idle through their remaining rows (shuffles need them all)
+  for (int q = q0; q < nIters; q += W) {
+    // prefetch: descriptors two iterations ahead, columns one iteration ahead
+    int4 m2[U];
+    int jn[U][CH];
+#pragma unroll
+    for (int u = 0; u < U; ++u) {
+      m2[u] = load_meta(q + 2 * W, u);
+#pragma unroll
+      for (int k = 0; k < CH; ++k) jn[u][k] = (m1[u].x >= 0 && m1[u].y + k < m1[u].z) ? col_ind[m1[u].y + k] : 0;
+    }
+    // everything that does not depend on the sweep: block rows, rhs (and the inverse diagonal), for all U groups
+    bool on[U];
+    double a[U][CH][NV], v[U], dinv[U][NV], mine[U][CH];
+#pragma unroll
+    for (int u = 0; u < U; ++u) {
+      on[u] = ok && m0[u].x >= 0;
+#pragma unroll
+      for (int k = 0; k < CH; ++k) {
+        const bool has = on[u] && m0[u].y + k < m0[u].z;
+        mine[u][k] = has ? ld_relaxed(out + (size_t)jj[u][k] * NV + r) : 0.0;
+#pragma unroll
+        for (int c = 0; c < NV; ++c) a[u][k][c] = has ? ILU[(size_t)(m0[u].y + k) * LPB + r * NV + c] : 0.0;
+      }
+      v[u] = on[u] ? in[(size_t)m0[u].x * NV + r] : 0.0;
+      if (!FORWARD) {
+#pragma unroll
+        for (int c = 0; c < NV; ++c) dinv[u][c] = on[u] ? invM[(size_t)m0[u].x * LPB + r * NV + c] : 0.0;
+      }
+    }
+    // lane r watches component r of every dependency of its rows; whatever is missing is looked at again, all of it
+    // per round, the warp as one instruction stream
+    for (unsigned spins = 0;; ++spins) {
+      bool miss = false;
+#pragma unroll
+      for (int u = 0; u < U; ++u)
+#pragma unroll
+        for (int k = 0; k < CH; ++k)
+          if ((unsigned long long)__double_as_longlong(mine[u][k]) == SENTINEL) {
+            miss = true;
+            mine[u][k] = ld_relaxed(out + (size_t)jj[u][k] * NV + r);
+          }
+      if (!__any_sync(FULLM, miss)) break;
+      if ((spins & 1023u) == 1023u) {
+        if (spins > (1u << 22)) atomicExch(ctrl + 1, 1);
+        if (__any_sync(FULLM, ld_relaxed_i(ctrl + 1) != 0)) { ok = false; break; }
+      }
+    }
+#pragma unroll
+    for (int u = 0; u < U; ++u) {
+#pragma unroll
+      for (int k = 0; k < CH; ++k) {
+        double y[NV];
+#pragma unroll
+        for (int c = 0; c < NV; ++c) y[c] = __shfl_sync(FULLM, mine[u][k], sub * NV + c);
+        if (on[u] && ok && m0[u].y + k < m0[u].z) {
+          double p = 0.0;
+#pragma unroll
+          for (int c = 0; c < NV; ++c) p += a[u][k][c] * y[c];
+          v[u] -= p;
+        }
+      }
+    }
+#pragma unroll
+    for (int u = 0; u < U; ++u) {
+      const int i = m0[u].x, kb = m0[u].y, ke = m0[u].z;
+      if (on[u]) {
+        for (int idx = kb + CH; idx < ke && ok; ++idx) {  // rows with more than CH entries on this side
+          const int j = col_ind[idx];
+          double p = 0.0;
+          for (int c = 0; c < NV && ok; ++c) {
+            double yj;
+            ok = poll(out + (size_t)j * NV + c, ctrl, yj);
+            p += ILU[(size_t)idx * LPB + r * NV + c] * yj;
+          }
+          v[u] -= p;
+        }
+      }
+      if (FORWARD) {
+        if (on[u] && ok) st_relaxed(out + (size_t)i * NV + r, v[u]);
+      } else {
+        double x = 0.0;
+#pragma unroll
+        for (int c = 0; c < NV; ++c) x += dinv[u][c] * __shfl_sync(FULLM, v[u], sub * NV + c);
+        if (on[u] && ok) st_relaxed(out + (size_t)i * NV + r, x);
+      }
+    }
+    ok = __all_sync(FULLM, ok);
+#pragma unroll
+    for (int u = 0; u < U; ++u) {
+      m0[u] = m1[u];
+      m1[u] = m2[u];
+#pragma unroll
+      for (int k = 0; k < CH; ++k) jj[u][k] = jn[u][k];
+    }
   }
 }
 
@@ -548,8 +692,8 @@ static void build_meta(LinSys& ls) {
   } else {
     make(ls.lvl_rows_lower.to_host(), true, ls.sweep_meta_lower);
     make(ls.lvl_rows_upper.to_host(), false, ls.sweep_meta_upper);
-    // k_poll_sweep_rows: 32/nVar rows per warp, every level padded to that
-    const int rpw = 32 / ls.nVar;
+    // k_poll_sweep_rowsU: ROWS_U groups of 32/nVar rows per warp and iteration, every level padded to that
+    const int rpw = ROWS_U * (32 / ls.nVar);
     auto pad = [&](const std::vector<int>& ptr, const std::vector<int>& rows, int& groups) {
       std::vector<int> p;
       p.reserve(rows.size() + (size_t)rpw * ptr.size());
@@ -590,7 +734,10 @@ template <int NV>
 static void ilu_apply_poll_impl(su2b200_ctx* c, LinSys& ls, const double* x, double* y, double* w) {
   const size_t n = (size_t)ls.Pd * NV;
   build_meta(ls);
-  SU2B_LAUNCH(c, k_fill_sentinel, (int)std::min<size_t>((n + 255) / 256, 148 * 8), 256, n, w, y);
+  // SU2B200_SWEEP_NOFILL=1 (timing experiment only, wrong results): without the sentinel fill every dependency is
+  // "there" at the first look (the values of the previous application), i.e. the sweeps run as pure streaming kernels
+  static const int nofill = getenv("SU2B200_SWEEP_NOFILL") ? atoi(getenv("SU2B200_SWEEP_NOFILL")) : 0;
+  if (!nofill) SU2B_LAUNCH(c, k_fill_sentinel, (int)std::min<size_t>((n + 255) / 256, 148 * 8), 256, n, w, y);
   const int4* ml = reinterpret_cast<const int4*>(ls.sweep_meta_lower.p);
   const int4* mu = reinterpret_cast<const int4*>(ls.sweep_meta_upper.p);
   const int* ci = ls.col_ind;
@@ -615,18 +762,29 @@ static void ilu_apply_poll_impl(su2b200_ctx* c, LinSys& ls, const double* x, dou
       // per row) -> k_poll_sweep_rows. Up to three launches per sweep, split at level boundaries.
       const int4* mrl = reinterpret_cast<const int4*>(ls.sweep_metar_lower.p);
       const int4* mru = reinterpret_cast<const int4*>(ls.sweep_metar_upper.p);
-      auto sweep = [&](auto narrowK, auto wideK, const int4* mnar, const int4* mwid, const int (&sp)[4], const double* ilu,
-                       const double* src, double* dst) {
+      // sp[1], sp[3] count padded units of ROWS_U groups (one consumer iteration of the wide kernel)
+      constexpr int UNIT = ROWS_U * (32 / NV);
+      static const int capU = getenv("SU2B200_SWEEP_BLOCKS_U") ? atoi(getenv("SU2B200_SWEEP_BLOCKS_U")) : 0;
+      static const int useU = getenv("SU2B200_SWEEP_U") ? atoi(getenv("SU2B200_SWEEP_U")) : ROWS_U;
+      auto sweep = [&](auto narrowK, auto wideK, auto wideK1, const int4* mnar, const int4* mwid, const int (&sp)[4],
+                       const double* ilu, const double* src, double* dst) {
         const int nRows = ls.Pd;
         if (sp[0] > 0) launch_resident(c, narrowK, (sp[0] + 3) / 4, capB, sp[0], mnar, ctrl, ci, ilu, invM, src, dst);
-        if (sp[3] > sp[1])
-          launch_resident(c, wideK, (sp[3] - sp[1] + 3) / 4, 0, sp[3] - sp[1], mwid + (size_t)sp[1] * (32 / NV), ctrl, ci,
-                          ilu, invM, src, dst);
+        if (sp[3] > sp[1]) {
+          if (useU == 1)  // A/B: one group per iteration over the same padded list (every unit is ROWS_U groups)
+            launch_resident(c, wideK1, ((sp[3] - sp[1]) * ROWS_U + 3) / 4, capU, (sp[3] - sp[1]) * ROWS_U,
+                            mwid + (size_t)sp[1] * UNIT, ctrl, ci, ilu, invM, src, dst);
+          else
+            launch_resident(c, wideK, (sp[3] - sp[1] + 3) / 4, capU, sp[3] - sp[1], mwid + (size_t)sp[1] * UNIT, ctrl, ci,
+                            ilu, invM, src, dst);
+        }
         if (nRows > sp[2])
           launch_resident(c, narrowK, (nRows - sp[2] + 3) / 4, capB, nRows - sp[2], mnar + sp[2], ctrl, ci, ilu, invM, src, dst);
       };
-      sweep(k_poll_sweep<NV, true>, k_poll_sweep_rows<NV, true>, ml, mrl, ls.poll_split_lower, ilu, x, w);
-      sweep(k_poll_sweep<NV, false>, k_poll_sweep_rows<NV, false>, mu, mru, ls.poll_split_upper, iluU, (const double*)w, y);
+      sweep(k_poll_sweep<NV, true>, k_poll_sweep_rowsU<NV, true, ROWS_U>, k_poll_sweep_rowsU<NV, true, 1>, ml, mrl,
+            ls.poll_split_lower, ilu, x, w);
+      sweep(k_poll_sweep<NV, false>, k_poll_sweep_rowsU<NV, false, ROWS_U>, k_poll_sweep_rowsU<NV, false, 1>, mu, mru,
+            ls.poll_split_upper, iluU, (const double*)w, y);
     } else if (pipe) {
       const size_t smem = (size_t)4 * PIPE * sizeof(SweepStage<NV>);
       launch_resident_smem(c, k_poll_sweep_pipe<NV, true>, smem, (ls.Pd + 3) / 4, capB, ls.Pd, ml, ctrl, ci, ilu, invM, x, w);

@@ -94,3 +94,80 @@ def test_in_place_preconditioner_application_and_repeated_builds():
             assert np.max(np.abs(z - zr)) <= 1e-12 * np.max(np.abs(zr))
     finally:
         ls.close()
+
+
+@pytest.mark.parametrize("n,tets", CASES)
+@pytest.mark.parametrize("nv", [4, 5])
+@pytest.mark.parametrize("wide,mode", [(1, 1), (1, 2), (8, 1), (40, 1)])
+def test_wide_level_kernels_match_the_oracle(n, tets, nv, wide, mode):
+    """The kernels that carry the benchmark -- k_poll_sweep_rows (wide-level ILU0 application) and k_factor_rows (wide-level
+    factorisation) -- only take levels of at least 4096 rows by default, wider than any level of a test mesh.  Here the
+    threshold is lowered (su2b200_linsys_set_wide_threshold) so that they run on the small tetrahedral and hexahedral
+    boxes: threshold 1 = every level, 8 / 40 = hybrid with a narrow head and tail; factor_mode 2 = rows kernel only."""
+    rng = np.random.default_rng(300 + nv + wide + (7 if tets else 0))
+    P, rp, ci, dp = _pattern(n, tets)
+    A = _matrix(rng, rp, ci, dp, nv)
+    x = rng.standard_normal(P * nv)
+    ilu, invM = lo.ilu0_build(rp, ci, dp, A)
+    zr = lo.ilu0_apply(rp, ci, dp, ilu, invM, x).ravel()
+    ls = LinearSystem(nv, P, P, rp, ci)
+    try:
+        ls.set_matrix(A)
+        ls.set_schedule(2, 2)
+        ls.BuildPreconditioner(capi.PREC_ILU)
+        z_default = ls.ApplyPreconditioner(capi.PREC_ILU, x)
+        ls.set_wide_threshold(wide, wide, mode)
+        ls.BuildPreconditioner(capi.PREC_ILU)
+        z = ls.ApplyPreconditioner(capi.PREC_ILU, x)
+        assert np.max(np.abs(z - zr)) <= 1e-12 * np.max(np.abs(zr))
+        assert np.max(np.abs(z - z_default)) <= 1e-14 * np.max(np.abs(zr))
+        b = rng.standard_normal(P * nv)
+        xs, it, res = ls.Solve(b, capi.SOLVER_FGMRES, capi.PREC_ILU, tol=1e-10, max_iter=30)
+        mv = lambda v: lo.block_spmv(rp, ci, A, v).ravel()
+        pc = lambda v: lo.ilu0_apply(rp, ci, dp, ilu, invM, v).ravel()
+        xo, ito, reso = lo.fgmres(mv, pc, b, 1e-10, 30)
+        assert it == ito
+        assert np.max(np.abs(xs - xo)) <= 1e-9 * np.max(np.abs(xo))
+    finally:
+        ls.close()
+
+
+def test_stale_slim_factors_are_refused():
+    """BuildILUPreconditioner / ComputeILUPreconditioner are separate entry points: with slim factors (U left in the
+    Jacobian) an application after the matrix changed would mix the old L, D with the new U -- it must fail loudly."""
+    rng = np.random.default_rng(11)
+    P, rp, ci, dp = _pattern([7, 6, 5], False)
+    ls = LinearSystem(5, P, P, rp, ci)
+    try:
+        ls.set_matrix(_matrix(rng, rp, ci, dp, 5))
+        ls.BuildPreconditioner(capi.PREC_ILU)
+        x = rng.standard_normal(P * 5)
+        ls.ApplyPreconditioner(capi.PREC_ILU, x)
+        ls.set_matrix(_matrix(rng, rp, ci, dp, 5))
+        with pytest.raises(capi.Su2B200Error, match="stale"):
+            ls.ApplyPreconditioner(capi.PREC_ILU, x)
+        ls.BuildPreconditioner(capi.PREC_ILU)
+        ls.ApplyPreconditioner(capi.PREC_ILU, x)
+    finally:
+        ls.close()
+
+
+def test_jacobi_and_lusgs_against_the_oracle():
+    """Jacobi (CSysMatrix.cpp:648-670) and LU-SGS (:826-888) preconditioners on the tetrahedral pattern."""
+    rng = np.random.default_rng(21)
+    P, rp, ci, dp = _pattern([6, 5, 4], True)
+    for nv in (4, 5):
+        A = _matrix(rng, rp, ci, dp, nv)
+        x = rng.standard_normal(P * nv)
+        ls = LinearSystem(nv, P, P, rp, ci)
+        try:
+            ls.set_matrix(A)
+            ls.BuildPreconditioner(capi.PREC_JACOBI)
+            z = ls.ApplyPreconditioner(capi.PREC_JACOBI, x).reshape(P, nv)
+            zr = np.stack([np.linalg.solve(A[dp[i]], x.reshape(P, nv)[i]) for i in range(P)])
+            assert np.max(np.abs(z - zr)) <= 1e-12 * np.max(np.abs(zr))
+            z = ls.ApplyPreconditioner(capi.PREC_LU_SGS, x).reshape(P, nv)
+            zr = lo.lusgs_apply(rp, ci, dp, A, x).reshape(P, nv)
+            assert np.max(np.abs(z - zr)) <= 1e-12 * np.max(np.abs(zr))
+        finally:
+            ls.close()

@@ -95,3 +95,29 @@ def test_halo_tables_exchange_over_gloo(world):
             msgs.append("worker timed out")
     assert not msgs, "\n".join(msgs)
     assert all(p.exitcode == 0 for p in procs)
+
+
+def test_selfcheck_compare_flags_a_divergent_rank():
+    """su2_b200.selfcheck.compare (the `multigpu_parity` summary of bench.py): slabs reassembled by global index."""
+    import numpy as np
+    from su2_b200.selfcheck import compare, slab_planes
+    assert slab_planes(13, 2) == [0, 6, 13] and slab_planes(25, 4) == [0, 6, 12, 18, 25]
+    rng = np.random.default_rng(3)
+    n, nv, k = 40, 5, 4
+    whole = dict(solution=rng.standard_normal((n, nv)), linsyssol=rng.standard_normal((n, nv)),
+                 rms=np.abs(rng.standard_normal((k, nv))), iters=np.array([5, 6, 6, 7]),
+                 CL=rng.standard_normal(k), CD=rng.standard_normal(k))
+    gid = rng.permutation(n)
+    owned = [gid[:17], gid[17:]]
+    pos = {int(g): i for i, g in enumerate(np.arange(n))}
+    def part(g, eps=0.0):
+        idx = np.array([pos[int(x)] for x in g])
+        return g, dict(solution=whole["solution"][idx] * (1 + eps), linsyssol=whole["linsyssol"][idx], rms=whole["rms"],
+                       iters=whole["iters"].copy(), CL=whole["CL"], CD=whole["CD"])
+    good = compare([part(owned[0]), part(owned[1])], np.arange(n), whole)
+    assert good["ok"] and good["max_rel"] == 0.0 and good["iters_equal"]
+    bad = compare([part(owned[0]), part(owned[1], 1e-6)], np.arange(n), whole)
+    assert not bad["ok"] and bad["max_rel"] > 1e-9
+    p0 = part(owned[0])
+    p0[1]["iters"][2] += 1
+    assert not compare([p0, part(owned[1])], np.arange(n), whole)["ok"]

@@ -63,3 +63,24 @@ def test_matrix_inverse_restatement():
     for n in (1, 4, 5):
         a = rng.standard_normal((n, n)) + n * np.eye(n)
         assert np.allclose(lo.matrix_inverse(a) @ a, np.eye(n), atol=1e-12)
+
+
+@pytest.mark.parametrize("variant,prec", [("naca0012_fgmres_lusgs", "lusgs"), ("naca0012_jacobi", "jacobi")])
+def test_lusgs_and_jacobi_restatements_match_reference_solution(variant, prec):
+    """The LU-SGS / Jacobi restatements inside the pinned FGMRES against the reference's solution of iteration 0 on the
+    C1 mesh (same Jacobian as naca0012_roe: only the preconditioner option differs)."""
+    base = load_golden(os.path.join(ROOT, "tests", "golden", "naca0012_roe.npz"))
+    gold = load_golden(os.path.join(ROOT, "tests", "golden", variant + ".npz"))
+    rp, ci, dp, A, nv, Pd = _system(base, it=0)
+    b = np.asarray(gold["it0_sys_linsysres"], dtype=np.float64).ravel()
+    assert np.array_equal(b, np.asarray(base["it0_sys_linsysres"]).ravel())
+    mv = lambda x: lo.block_spmv(rp, ci, A, x, Pd).ravel()
+    if prec == "lusgs":
+        pc = lambda x: lo.lusgs_apply(rp, ci, dp, A, x, Pd).ravel()
+    else:
+        inv = np.stack([lo.matrix_inverse(A[dp[i]]) for i in range(Pd)])
+        pc = lambda x: np.einsum("ijk,ik->ij", inv, x.reshape(-1, nv)).ravel()
+    x, it, res = lo.fgmres(mv, pc, b, float(gold["cfg_linear_tol"]), int(gold["cfg_linear_iter"]), Pd * nv)
+    ref = np.asarray(gold["it0_linsyssol"], dtype=np.float64).ravel()
+    assert it == int(gold["it0_linsol_iter"])
+    assert np.max(np.abs(x - ref)) <= 1e-8 * np.max(np.abs(ref))

@@ -23,6 +23,15 @@ TOL = {  # stage -> relative tolerance
 }
 
 
+def _tol(tol, key):
+    """Tolerance of a report entry; per-variable entries ("stage/var", parity_util.relerr_var) get 1000x the stage's
+    (1e-9 where the global measure is held to 1e-12: measured worst case 2.7e-10, the wall-normal momentum residual of the
+    stretched wing-box, a component formed by cancellation of terms 1e3 times larger)."""
+    if key.endswith("/var"):
+        return 1000.0 * tol.get(key[:-4], tol["default"])
+    return tol.get(key, tol["default"])
+
+
 def _gold(name):
     p = os.path.join(ROOT, "tests", "golden", name + ".npz")
     if not os.path.exists(p):
@@ -46,7 +55,7 @@ def test_iteration_stage_by_stage(case):
         run_first_iteration(s, gold, it, report)
         s.close()
         print(case, "it", it, {k: ("%.2e" % v if isinstance(v, float) else v) for k, v in report.items()})
-        bad = {k: v for k, v in report.items() if isinstance(v, float) and not (v <= TOL.get(k, TOL["default"]))}
+        bad = {k: v for k, v in report.items() if isinstance(v, float) and not (v <= _tol(TOL, k))}
         assert not bad, (it, bad)
         got, ref = report["linsol_iter"]
         assert got == ref, (it, got, ref)
@@ -89,7 +98,7 @@ def test_rans_sa_stage_by_stage(case):
         # in both codes, so the flow right-hand side and its Krylov solution are not comparable there
         noise = ("bc_residual", "rhs", "res_rms", "linsyssol", "post_solution") if it == 0 else ()
         bad = {k: v for k, v in report.items()
-               if isinstance(v, float) and k not in noise and not (v <= tol.get(k, tol["default"]))}
+               if isinstance(v, float) and k.split("/")[0] not in noise and not (v <= _tol(tol, k))}
         assert not bad, (it, bad)
 
 
@@ -101,8 +110,9 @@ def test_rans_sa_history(case):
     reps = s.iterate(n)
     s.close()
     hist = gold["history"]
+    nv = s.nVar
     for i, r in enumerate(reps):
-        ref_rms = hist[i, :5]
+        ref_rms = hist[i, :nv]
         if np.max(np.abs(ref_rms)) < 1e-14:
             continue  # uniform free stream: the flow residual of iteration 0 is round-off in both codes
         ok = np.abs(r["rms_flow"] - ref_rms) <= 1e-6 * np.abs(ref_rms) + 1e-12 * np.max(np.abs(ref_rms))
@@ -129,7 +139,7 @@ def test_linear_solver_and_gradient_variants(case):
     if case == "naca0012_ls":
         assert "grad_recon" in report and "limiter" in report
     tol = dict(TOL)
-    bad = {k: v for k, v in report.items() if isinstance(v, float) and not (v <= tol.get(k, tol["default"]))}
+    bad = {k: v for k, v in report.items() if isinstance(v, float) and not (v <= _tol(tol, k))}
     assert not bad, bad
     got, ref = report["linsol_iter"]
     assert got == ref, (got, ref)
@@ -161,7 +171,7 @@ def test_colored_assembly_matches_the_reference(case):
     run_first_iteration(s, gold, it, report)
     s.close()
     print(case, "colored", {k: ("%.2e" % v if isinstance(v, float) else v) for k, v in report.items()})
-    bad = {k: v for k, v in report.items() if isinstance(v, float) and not (v <= TOL.get(k, TOL["default"]))}
+    bad = {k: v for k, v in report.items() if isinstance(v, float) and not (v <= _tol(TOL, k))}
     assert not bad, bad
     assert report["linsol_iter"][0] == report["linsol_iter"][1]
 
@@ -173,7 +183,7 @@ def test_rans_colored_assembly():
     s.close()
     hist = gold["history"]
     for i, r in enumerate(reps[1:], start=1):
-        assert np.allclose(r["rms_flow"], hist[i, :5], rtol=1e-6, atol=1e-12 * np.max(np.abs(hist[i, :5])))
+        assert np.allclose(r["rms_flow"], hist[i, :5], rtol=1e-6, atol=1e-12 * np.max(np.abs(hist[i, :5]))), (i, r, hist[i])
         assert abs(r["rms_turb"] - hist[i, 5]) <= 1e-6 * abs(hist[i, 5])
         assert r["linsol_iter_flow"] == int(hist[i, 8]) and r["linsol_iter_turb"] == int(hist[i, 10])
 

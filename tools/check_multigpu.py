@@ -4,7 +4,11 @@ torchrun --nproc-per-node N tools/check_multigpu.py [EULER|NAVIER_STOKES|RANS|EU
 Every rank assembles the residual of iteration 0 on its slab (halo exchange of solution, gradients, limiters, nu~);
 rank 0 also runs the undivided mesh and compares, by global point index, the rhs vector, the local time steps, the
 limiters and the rms residuals: they must agree to round-off (the preconditioner is the only rank-dependent part of an
-iteration, and it comes after). Prints `multigpu parity: max rel diff = X` and exits 0 iff X <= 1e-12."""
+iteration, and it comes after). Prints `multigpu parity: max rel diff = X` and exits 0 iff X <= 1e-12.
+
+With ITER_<kind> (ITER_RANS, ITER_EULER, ITER_NAVIER_STOKES) the check covers WHOLE iterations instead
+(su2_b200/selfcheck.py): 5 iterations on N slabs against the undivided mesh with N block-Jacobi partitions cut at the
+slab boundaries -- equal Krylov iteration counts, rms 1e-8, LinSysSol / Solution 1e-9, CL / CD 1e-6."""
 import os, sys
 import numpy as np
 import torch
@@ -64,12 +68,43 @@ def first_iteration(opts, rank, world, device, comm=None):
     return gid[:Pd], out
 
 
+def whole_iterations(kind, rank, world, local):
+    from su2_b200.selfcheck import whole_iteration_parity
+    n_planes = 6 * world + 1
+    text = bench.make_cfg(kind, [12, 10, n_planes], 1)
+
+    def comm(s):
+        idbuf = torch.zeros(128, dtype=torch.uint8, device="cuda")
+        if rank == 0:
+            idbuf.copy_(torch.from_numpy(s.comm_unique_id()).cuda())
+        dist.broadcast(idbuf, 0)
+        return idbuf.cpu().numpy()
+
+    def gather(obj):
+        parts = [None] * world
+        dist.all_gather_object(parts, obj)
+        return parts
+
+    res = whole_iteration_parity(text, n_planes, 5, rank, world, local, comm, gather)
+    ok = 1.0
+    if rank == 0:
+        print("multigpu parity, whole iterations (%s, %d ranks): %s" % (kind, world, res))
+        ok = 1.0 if res["ok"] else 0.0
+    flag = torch.tensor([ok], device="cuda")
+    dist.broadcast(flag, 0)
+    return flag.item() == 1.0
+
+
 def main():
     kind = sys.argv[1] if len(sys.argv) > 1 else "RANS"
     rank, world = int(os.environ.get("RANK", 0)), int(os.environ.get("WORLD_SIZE", 1))
     local = int(os.environ.get("LOCAL_RANK", 0))
     torch.cuda.set_device(local)
     dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+    if kind.startswith("ITER_"):
+        ok = whole_iterations(kind[5:], rank, world, local)
+        dist.destroy_process_group()
+        sys.exit(0 if ok else 1)
     n = [12, 10, 8 * world + 1]
     jst = kind.endswith("_JST")
     text = bench.make_cfg(kind[:-4] if jst else kind, n, 1)
