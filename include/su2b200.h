@@ -222,6 +222,17 @@ typedef struct {
   int prec_partitions;               /* <=1: level-scheduled ILU0/LU-SGS == the reference's serial sweeps;
                                         K>1: K nnz-balanced row partitions, block-Jacobi between them, exactly what the
                                         reference does with LINEAR_SOLVER_PREC_THREADS=K (CSysMatrix.cpp:199-227,701-711) */
+  int turb_reducer;                  /* CScalarSolver::ReducerStrategy (CScalarSolver.inl:59): with it the two one-sided
+                                        SA diffusion Jacobians of an edge are AVERAGED into the off-diagonal blocks and
+                                        the diagonal is minus the column sum (CScalarSolver.hpp:196-203, .inl:318-320).
+                                        The reference switches it on when the "colouring efficiency" it computes for
+                                        the scalar solver is below 0.875 -- in a serial run that is
+                                        nEdge / (512 ceil(nEdge/512)) (CGeometry.cpp:3826, graph_toolbox.hpp:661), so
+                                        small meshes with an unlucky edge count get it. 1 / 0 = on / off, -1 = that rule */
+  /* FAS multigrid (CMultiGridIntegration): the level this context represents */
+  int mg_level;                      /* 0 = finest grid; > 0: agglomerated level (no MUSCL, no JST sensor/Laplacian:
+                                        CEulerSolver.cpp:1584-1586, :1662; centred schemes use CLaxScheme, CNumericsSIMD.cpp:70) */
+  double lax_kappa1;                 /* LAX_SENSOR_COEFF (CLaxScheme, centered.hpp:474-530): 1st-order dissipation of the coarse levels */
 } su2b200_flow_config;
 
 int su2b200_flow_configure(su2b200_ctx* ctx, const su2b200_flow_config* cfg);

@@ -120,6 +120,10 @@ class CB200FlowBackend {
     B200_CHECK(su2b200_array_download(flowCtx, SU2B200_ARR_SOLUTION, buf.data()));
     for (unsigned long i = 0; i < nPoint; ++i)
       for (unsigned short v = 0; v < nVar; ++v) flow->GetNodes()->SetSolution(i, v, buf[i * nVar + v]);
+    /*--- the scalar solvers take their time step from the flow solver's (CScalarSolver::SetTime_Step) ---*/
+    std::vector<double> dt(nPoint);
+    B200_CHECK(su2b200_array_download(flowCtx, SU2B200_ARR_DELTA_TIME, dt.data()));
+    for (unsigned long i = 0; i < nPoint; ++i) flow->GetNodes()->SetDelta_Time(i, dt[i]);
     (void)nDim;
     if (linRes) *linRes = res;
     return iters;
@@ -263,6 +267,7 @@ class CB200FlowBackend {
     f.aoa_deg = val(c->GetAoA()); f.aos_deg = val(c->GetAoS()); f.ref_area = val(c->GetRefArea()); f.ref_length = val(c->GetRefLength());
     f.ref_origin[0] = val(c->GetRefOriginMoment_X(0)); f.ref_origin[1] = val(c->GetRefOriginMoment_Y(0)); f.ref_origin[2] = val(c->GetRefOriginMoment_Z(0));
     f.assembly = SU2B200_ASSEMBLY_GATHER; f.prec_partitions = 1;
+    f.turb_reducer = -1; f.mg_level = 0; f.lax_kappa1 = val(c->GetKappa_1st_Flow());
     if (f.rans_sa) {  /*--- free-stream eddy viscosity of the CTurbSASolver constructor (CTurbSASolver.cpp:100-134) ---*/
       const double mu = val(c->GetViscosity_FreeStreamND());
       const double chi = f.nu_tilde_inf / (mu / f.density_inf);

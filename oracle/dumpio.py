@@ -95,7 +95,9 @@ def config_from_dump(d):
         turb_linear_solver=sol[d["cfg_linear_solver"]], turb_linear_prec=pre[d["cfg_linear_prec"]],
         turb_linear_tol=d["cfg_linear_tol"], turb_linear_iter=int(d["cfg_linear_iter"]),
         aoa_deg=d["cfg_aoa"], aos_deg=d["cfg_aos"], ref_area=d["cfg_ref_area"], ref_length=d["cfg_ref_length"],
-        ref_origin=list(d["cfg_ref_origin"]))
+        ref_origin=list(d["cfg_ref_origin"]),
+        # CScalarSolver::ReducerStrategy of the run that made the fixture (dumped by newer fixtures; else the rule applies)
+        turb_reducer=int(d.get("cfg_turb_reducer", -1)))
     if kw["rans_sa"]:
         # free-stream eddy viscosity of the CTurbSASolver constructor (CTurbSASolver.cpp:100-134)
         t = kw["temperature_inf"]

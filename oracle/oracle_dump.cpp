@@ -183,6 +183,8 @@ class Dumper : public CSinglezoneDriver {
     w.iscalar("cfg_viscous", c->GetViscous());
     w.iscalar("cfg_rans_sa", c->GetKind_Turb_Model() == TURB_MODEL::SA);
     w.iscalar("cfg_sa_negative", c->GetSAParsedOptions().version == SA_OPTIONS::NEG);
+    if (c->GetKind_Turb_Model() == TURB_MODEL::SA)  // averaged SA diffusion Jacobians (CScalarSolver.inl:59)
+      w.iscalar("cfg_turb_reducer", static_cast<CTurbSASolver*>(solver_container[ZONE_0][INST_0][MESH_0][TURB_SOL])->ReducerStrategy);
     w.scalar("cfg_mu_ref", c->GetMu_RefND()); w.scalar("cfg_mu_temperature_ref", c->GetMu_Temperature_RefND());
     w.scalar("cfg_mu_sutherland", c->GetMu_SND()); w.scalar("cfg_mu_constant", c->GetMu_ConstantND());
     w.iscalar("cfg_viscosity_model_sutherland", c->GetKind_ViscosityModel() == VISCOSITYMODEL::SUTHERLAND);

@@ -53,7 +53,8 @@ class FlowConfig(C.Structure):
         ("turb_linear_tol", C.c_double),
         ("aoa_deg", C.c_double), ("aos_deg", C.c_double), ("ref_area", C.c_double), ("ref_length", C.c_double),
         ("ref_origin", C.c_double * 3),
-        ("assembly", C.c_int), ("prec_partitions", C.c_int),
+        ("assembly", C.c_int), ("prec_partitions", C.c_int), ("turb_reducer", C.c_int),
+        ("mg_level", C.c_int), ("lax_kappa1", C.c_double),
     ]
 
 

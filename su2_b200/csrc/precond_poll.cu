@@ -315,7 +315,7 @@ __global__ void __launch_bounds__(128) k_poll_sweep_pipe(int n, const int4* __re
 #define ROWS_CH 3
 #endif
 #ifndef ROWS_U
-#define ROWS_U 2  // row groups per warp and iteration of the wide-level kernel (k_poll_sweep_rowsU); levels are padded to it
+#define ROWS_U 1  // row groups per warp and iteration of the wide-level kernel (k_poll_sweep_rowsU); levels are padded to it
 #endif
 #ifndef ROWS_MIN_BLOCKS
 #define ROWS_MIN_BLOCKS 5
@@ -412,20 +412,19 @@ __global__ void __launch_bounds__(128, ROWS_MIN_BLOCKS) k_poll_sweep_rows(int nG
   }
 }
 
-// ---- the same mapping, U row groups per warp and iteration -----------------------------------------------------------------
-// What bounds the wide levels (measured, 185^3, RCM order; profiles/r02_ilu_apply_ab.txt): the sweep is a chain of 553
-// levels per direction, and a level of n rows takes ceil(n / R) consumer iterations of ~1.2 us each, R = rows in flight
-// = SMs * resident warps * rows per warp. Six variants with 8..20 resident warps per SM all fall on
-//     t = 1.96 ms + 16.8 ms / (warps per SM)        [= 2 tau (L + N / R), tau = 1.18 us, L = 553 levels, N = 6.33 M rows],
-// whether the factor entries come through registers or through a cp.async ring two or three groups deep (the ring
-// variants were slower only because their shared memory left 12-16 warps resident instead of 20), and looking at the
-// next group's dependencies one iteration early changed nothing (a warp's next group sits a whole wave further on,
-// i.e. mostly in the NEXT level, whose dependencies are still being produced). So the lever is R: with U = 2 groups of
-// the same level per iteration, handled as one interleaved instruction stream, 16 warps * 12 rows * 148 SMs = 28 k rows
-// are in flight -- more than the widest level (25.6 k) -- and every level costs ONE round trip. Levels are padded to
-// U * 32/nVar rows, so the groups of an iteration never depend on one another. Descriptors run two iterations ahead
-// and columns one iteration ahead in registers, which also takes the descriptor -> columns part off the latency chain
-// of an iteration. Same arithmetic in the same order as k_poll_sweep_rows: bit-identical results.
+// ---- the same mapping with descriptors and columns prefetched, U row groups per warp and iteration -------------------------
+// What bounds the wide levels (measured on the 185^3 RANS matrix, RCM order; profiles/r02_ilu_apply_ab.txt):
+//   * run WITHOUT the sentinel fill (every dependency "there" at the first look, i.e. as pure streaming kernels) one
+//     application takes 2.10 ms = 5.2 TB/s on the algorithmic bytes (1.99 ms with every level in this kernel): that is
+//     the bandwidth bound of this data layout (600 of every 1400 bytes of a block row are read per sweep);
+//   * with the dependencies it takes 2.78 ms: the chain of 2 x 553 levels adds 0.68 ms (0.6 us per level, one L2 round
+//     trip), and nothing tried moves it: a cp.async ring two/three groups deep (3.0-3.6 ms, fewer resident warps),
+//     looking at the next group's dependencies one iteration early (3.2 ms: a warp's next group sits a whole wave
+//     further on, mostly in the NEXT level), U = 2 or 3 groups per iteration as one instruction stream (2.86-3.5 ms),
+//     20 instead of 16 resident warps (2.77 ms), level-width thresholds 256...4096 (2.94-2.97 ms at U = 2).
+// Shipped: U = 1, descriptors two iterations and columns one iteration ahead in registers (the descriptor -> columns
+// part of the latency chain of an iteration is gone), 16 resident warps per SM. Same arithmetic in the same order as
+// k_poll_sweep_rows: bit-identical results.
 #ifndef ROWSU_MIN_BLOCKS
 #define ROWSU_MIN_BLOCKS 4
 #endif

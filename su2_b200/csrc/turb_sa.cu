@@ -42,7 +42,7 @@ __host__ __device__ inline SAConst sa_constants() {
 // ---- edge kernel: convection (first-order upwind) + non-conservative diffusion evaluated from both sides ---------
 template <int ND>
 __global__ void __launch_bounds__(128)
-k_turb_edge(int E, int neg, const int* __restrict__ ei, const int* __restrict__ ej, const double* __restrict__ enormal,
+k_turb_edge(int E, int neg, int reducer, const int* __restrict__ ei, const int* __restrict__ ej, const double* __restrict__ enormal,
             const double* __restrict__ coord, const double* __restrict__ V, const double* __restrict__ nu,
             const double* __restrict__ gnu, const int* __restrict__ eij, const int* __restrict__ eji,
             double* __restrict__ A, double* __restrict__ ef /* SoA [7][E]: F, Rij, Rji, a0, Jij_i, a1, Jji_i */) {
@@ -104,12 +104,27 @@ k_turb_edge(int E, int neg, const int* __restrict__ ei, const int* __restrict__ 
   };
   diffusion(lam_i, lam_j, nui, nuj, projC_ij, Rij, Jij_i, Jij_j);
   diffusion(lam_j, lam_i, nuj, nui, projC_ji, Rji, Jji_i /* w.r.t. j */, Jji_j /* w.r.t. i */);
-  // off-diagonals: UpdateBlocks overwrites (B_ij = a1, B_ji = -a0), then the diffusion terms are subtracted
-  A[eij[e]] = a1 - Jij_j;
-  A[eji[e]] = -a0 - Jji_j;
   ef[(size_t)0 * E + e] = F;
   ef[(size_t)1 * E + e] = Rij;
   ef[(size_t)2 * E + e] = Rji;
+  if (reducer) {
+    // ReducerStrategy (CScalarSolver.hpp:196-203, :219-226): the Jacobians of the two one-sided evaluations are averaged
+    // into the off-diagonal blocks, the diagonal is minus the column sum (SetDiagonalAsColumnSum, CScalarSolver.inl:320):
+    // point i receives -B_ji, point j receives -B_ij (k_turb_point adds ef[3] - ef[4] for the first node of an edge and
+    // subtracts ef[5] + ef[6] for the second)
+    const double Bij = a1 - 0.5 * Jij_j + 0.5 * Jji_i;
+    const double Bji = -a0 + 0.5 * Jij_i - 0.5 * Jji_j;
+    A[eij[e]] = Bij;
+    A[eji[e]] = Bji;
+    ef[(size_t)3 * E + e] = -Bji;
+    ef[(size_t)4 * E + e] = 0.0;
+    ef[(size_t)5 * E + e] = Bij;
+    ef[(size_t)6 * E + e] = 0.0;
+    return;
+  }
+  // off-diagonals: UpdateBlocks overwrites (B_ij = a1, B_ji = -a0), then the diffusion terms are subtracted
+  A[eij[e]] = a1 - Jij_j;
+  A[eji[e]] = -a0 - Jji_j;
   ef[(size_t)3 * E + e] = a0;
   ef[(size_t)4 * E + e] = Jij_i;
   ef[(size_t)5 * E + e] = a1;
@@ -326,14 +341,18 @@ void turb_space_integration(su2b200_ctx* c) {
   auto& ls = c->sys[1];
   SU2B_REQUIRE(g.wall_dist.n == (size_t)g.P, "RANS needs CPoint::Wall_Distance (geometry_desc.wall_distance)");
   const int neg = c->cfg.sa_negative;
+  // the reference's serial rule for CScalarSolver::ReducerStrategy (see su2b200_flow_config::turb_reducer)
+  const int reducer = c->cfg.turb_reducer >= 0
+                          ? c->cfg.turb_reducer
+                          : ((double)g.E / (512.0 * (double)((g.E + 511) / 512)) < 0.875 ? 1 : 0);
   if (s.turb_edge_flux.n < (size_t)7 * g.E) s.turb_edge_flux.alloc((size_t)7 * g.E);
   {
     ProfScope prof_(c, PROF_TURB_EDGE);
     if (g.nDim == 2)
-      SU2B_LAUNCH(c, k_turb_edge<2>, nblk(g.E, 128), 128, g.E, neg, g.edge_i.p, g.edge_j.p, g.edge_normal.p, g.coord.p,
+      SU2B_LAUNCH(c, k_turb_edge<2>, nblk(g.E, 128), 128, g.E, neg, reducer, g.edge_i.p, g.edge_j.p, g.edge_normal.p, g.coord.p,
                   s.V.p, s.nu.p, s.nu_grad.p, g.edge_ij.p, g.edge_ji.p, ls.A.p, s.turb_edge_flux.p);
     else
-      SU2B_LAUNCH(c, k_turb_edge<3>, nblk(g.E, 128), 128, g.E, neg, g.edge_i.p, g.edge_j.p, g.edge_normal.p, g.coord.p,
+      SU2B_LAUNCH(c, k_turb_edge<3>, nblk(g.E, 128), 128, g.E, neg, reducer, g.edge_i.p, g.edge_j.p, g.edge_normal.p, g.coord.p,
                   s.V.p, s.nu.p, s.nu_grad.p, g.edge_ij.p, g.edge_ji.p, ls.A.p, s.turb_edge_flux.p);
   }
   {

@@ -398,4 +398,5 @@ def default_config():
     c.turb_linear_solver, c.turb_linear_prec, c.turb_linear_tol, c.turb_linear_iter = capi.SOLVER_FGMRES, capi.PREC_ILU, 1e-6, 10
     c.ref_area, c.ref_length = 1.0, 1.0
     c.assembly, c.prec_partitions = capi.ASSEMBLY_GATHER, 1
+    c.turb_reducer, c.mg_level, c.lax_kappa1 = -1, 0, 0.15
     return c
