@@ -70,6 +70,7 @@ enum {
   SU2B200_ARR_ILU = 15,          /* CSysMatrix::ILU_matrix         [nnz][nVar][nVar]    */
   SU2B200_ARR_INVM = 16,         /* CSysMatrix::invM               [Pd][nVar][nVar]     */
   SU2B200_ARR_UNDER_RELAX = 17,  /* CVariable::UnderRelaxation     [P]                  */
+  SU2B200_ARR_RES_TRUNC = 18,    /* CVariable::Res_TruncError      [P][nVar] (multigrid forcing term; empty without) */
   SU2B200_ARR_TURB_SOLUTION = 20,/* CTurbSAVariable::Solution      [P][1]               */
   SU2B200_ARR_TURB_GRADIENT = 21,/* CScalarVariable::Gradient      [P][1][nDim]         */
   SU2B200_ARR_TURB_LINSYSRES = 22,
@@ -300,6 +301,38 @@ typedef struct {
   unsigned long nonphysical_points, nonphysical_edges;
 } su2b200_iter_report;
 int su2b200_iterate(su2b200_ctx* ctx, int nIter, su2b200_iter_report* reports /*[nIter], may be NULL*/);
+
+/* ---- FAS multigrid: CMultiGridIntegration (SU2_CFD/src/integration/CMultiGridIntegration.cpp) ---------------------
+ * One context per level: level 0 is the finest grid, level k > 0 an agglomerated grid uploaded like any other geometry
+ * (CMultiGridGeometry is host preprocessing outside the hot path) and configured with mg_level = k (first-order upwind /
+ * CLaxScheme, no JST sensor, its own CFL: CConfig::GetCFL(iMesh)). All levels on one device, single rank. */
+/* CPoint::Children_CV of the coarse level: children_ptr[nPointCoarse+1], children[] = points of `fine` */
+int su2b200_mg_link(su2b200_ctx* fine, su2b200_ctx* coarse, const unsigned long* children_ptr,
+                    const unsigned long* children);
+/* SetRestricted_Solution (:563-608): coarse Solution = volume-weighted average of the children, zero velocity on no-slip walls */
+int su2b200_mg_set_restricted_solution(su2b200_ctx* fine, su2b200_ctx* coarse);
+/* SetResidual_Term (:552-561): LinSysRes += Res_TruncError */
+int su2b200_mg_set_residual_term(su2b200_ctx* ctx);
+/* SetForcing_Term (:502-550): coarse Res_TruncError = damp * sum of the children's LinSysRes - coarse LinSysRes */
+int su2b200_mg_set_forcing_term(su2b200_ctx* fine, su2b200_ctx* coarse, double damp_restriction);
+/* GetProlongated_Correction (:308-381): coarse Solution_Old = u_c - I(u_f); fine LinSysRes(child) = that correction */
+int su2b200_mg_get_prolongated_correction(su2b200_ctx* fine, su2b200_ctx* coarse);
+/* SmoothProlongated_Correction (:383-456): nSmooth Jacobi sweeps over the neighbours, boundary points restored */
+int su2b200_mg_smooth_prolongated_correction(su2b200_ctx* ctx, int nSmooth, double coeff);
+/* SetProlongated_Correction (:458-484): Solution += damp * LinSysRes over the owned points */
+int su2b200_mg_set_prolongated_correction(su2b200_ctx* ctx, double damp_prolongation);
+typedef struct {
+  int nLevels;                 /* number of COARSE levels (CConfig::GetnMGLevels)                                */
+  int cycle;                   /* MGCYCLE: 0 V_CYCLE, 1 W_CYCLE, 2 FULLMG_CYCLE (runs as V)                      */
+  int pre_smooth[8];           /* MG_PRE_SMOOTH per level                                                        */
+  int post_smooth[8];          /* MG_POST_SMOOTH                                                                 */
+  int correction_smooth[8];    /* MG_CORRECTION_SMOOTH                                                           */
+  double damp_restriction;     /* MG_DAMP_RESTRICTION                                                            */
+  double damp_prolongation;    /* MG_DAMP_PROLONGATION                                                           */
+} su2b200_mg_config;
+/* CMultiGridIntegration::MultiGrid_Iteration (:37-127) + MultiGrid_Cycle (:129-300): nIter FAS cycles over
+ * levels[0..nLevels], forces and residual norms of the finest grid in the reports */
+int su2b200_mg_iterate(su2b200_ctx** levels, const su2b200_mg_config* cfg, int nIter, su2b200_iter_report* reports);
 
 /* ---- CSysMatrix / CSysVector / CSysSolve level (host-buffer entry points, HtD/DtH inside) ---- */
 

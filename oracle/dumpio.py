@@ -50,13 +50,15 @@ def load_golden(path):
     return out
 
 
-def geometry_from_dump(d):
-    g = {k: d[k] for k in ("nDim", "nPoint", "nPointDomain", "nEdge", "edge_nodes", "edge_normal", "coord", "volume",
-                           "point_ptr", "point_nbr", "point_edge", "row_ptr", "col_ind", "dia_ptr", "edge_ptr",
-                           "nNeighbor", "physical_boundary", "wall_distance")}
+def geometry_from_dump(d, level=0):
+    """CGeometry arrays of the finest grid (level 0) or of agglomerated multigrid level `level` ("mg<level>_" keys)."""
+    G = "" if level == 0 else "mg%d_" % level
+    g = {k: d[G + k] for k in ("nDim", "nPoint", "nPointDomain", "nEdge", "edge_nodes", "edge_normal", "coord", "volume",
+                               "point_ptr", "point_nbr", "point_edge", "row_ptr", "col_ind", "dia_ptr", "edge_ptr",
+                               "nNeighbor", "physical_boundary", "wall_distance")}
     markers = []
-    for m in range(int(d["nMarker"])):
-        p = "marker%d_" % m
+    for m in range(int(d[G + "nMarker"])):
+        p = G + "marker%d_" % m
         markers.append(dict(kind=int(d[p + "kind"]), node=d[p + "node"], normal=d[p + "normal"],
                             normal_neighbor=d[p + "normal_neighbor"], sym_unit_normal=d[p + "sym_unit_normal"],
                             monitoring=int(d[p + "monitoring"]), heat_flux=float(d[p + "heat_flux"]), tag=d[p + "tag"]))

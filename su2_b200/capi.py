@@ -58,6 +58,13 @@ class FlowConfig(C.Structure):
     ]
 
 
+class MgConfig(C.Structure):
+    _fields_ = [
+        ("nLevels", C.c_int), ("cycle", C.c_int), ("pre_smooth", C.c_int * 8), ("post_smooth", C.c_int * 8),
+        ("correction_smooth", C.c_int * 8), ("damp_restriction", C.c_double), ("damp_prolongation", C.c_double),
+    ]
+
+
 class IterReport(C.Structure):
     _fields_ = [
         ("rms_flow", C.c_double * 5), ("rms_turb", C.c_double), ("CL", C.c_double), ("CD", C.c_double),
@@ -79,7 +86,7 @@ ASSEMBLY_GATHER, ASSEMBLY_COLORED = 0, 1
 ARR = dict(
     SOLUTION=0, SOLUTION_OLD=1, PRIMITIVE=2, GRAD_RECON=3, GRAD_PRIM=4, LIMITER=5, DELTA_TIME=6, LINSYSRES=7,
     LINSYSSOL=8, JACOBIAN=9, LAMBDA=10, SENSOR=11, UND_LAPL=12, MAX_LAMBDA_INV=13, MAX_LAMBDA_VISC=14, ILU=15,
-    INVM=16, UNDER_RELAX=17, TURB_SOLUTION=20, TURB_GRADIENT=21, TURB_LINSYSRES=22, TURB_LINSYSSOL=23,
+    INVM=16, UNDER_RELAX=17, RES_TRUNC=18, TURB_SOLUTION=20, TURB_GRADIENT=21, TURB_LINSYSRES=22, TURB_LINSYSSOL=23,
     TURB_JACOBIAN=24, EDDY_VISC=25, VORTICITY=26, STRAIN_MAG=27, WALL_DIST=28, TURB_DELTA_TIME=29,
     TURB_SOLUTION_OLD=30)
 
@@ -98,7 +105,9 @@ EXPORTED_SYMBOLS = [
     "su2b200_linsys_set_partitions", "su2b200_linsys_set_schedule", "su2b200_linsys_set_wide_threshold",
     "su2b200_linsys_set_partition_rows", "su2b200_linsys_set_matrix", "su2b200_linsys_spmv",
     "su2b200_linsys_build_preconditioner", "su2b200_linsys_apply_preconditioner", "su2b200_linsys_solve",
-    "su2b200_vector_dot", "su2b200_comm_unique_id", "su2b200_comm_init", "su2b200_halo_exchange",
+    "su2b200_vector_dot", "su2b200_mg_link", "su2b200_mg_set_restricted_solution", "su2b200_mg_set_residual_term",
+    "su2b200_mg_set_forcing_term", "su2b200_mg_get_prolongated_correction", "su2b200_mg_smooth_prolongated_correction",
+    "su2b200_mg_set_prolongated_correction", "su2b200_mg_iterate", "su2b200_comm_unique_id", "su2b200_comm_init", "su2b200_halo_exchange",
     "su2b200_timer_start", "su2b200_timer_stop", "su2b200_launch_count", "su2b200_bench_edge_kernel",
     "su2b200_bench_spmv", "su2b200_bench_prec", "su2b200_struct_sizes",
     "su2b200_mesh_create_box", "su2b200_mesh_read_su2", "su2b200_mesh_write_su2", "su2b200_mesh_stretch", "su2b200_mesh_destroy", "su2b200_mesh_set_marker",

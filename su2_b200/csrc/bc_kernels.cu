@@ -146,7 +146,7 @@ __global__ void k_bc_far_field(int nV, int Pd, FlowParams p, FarFieldInf inf, co
 template <int ND>
 __global__ void k_bc_sym_plane(int nV, int Pd, const int* __restrict__ vnode, const double* __restrict__ unit,
                                const int* __restrict__ row_ptr, double* __restrict__ U_old, double* __restrict__ res,
-                               double* __restrict__ A) {
+                               double* __restrict__ A, double* __restrict__ trunc) {
   constexpr int NV = ND + 2;
   const int t = blockIdx.x * blockDim.x + threadIdx.x;
   if (t >= nV) return;
@@ -155,6 +155,13 @@ __global__ void k_bc_sym_plane(int nV, int Pd, const int* __restrict__ vnode, co
   double n[ND];
 #pragma unroll
   for (int d = 0; d < ND; ++d) n[d] = unit[(size_t)t * ND + d];
+  if (trunc) {  // "Correction for multigrid" (CFVMFlowSolverBase.inl:1260-1268): the forcing term loses its normal momentum
+    double nt = 0.0;
+#pragma unroll
+    for (int d = 0; d < ND; ++d) nt += trunc[(size_t)i * NV + 1 + d] * n[d];
+#pragma unroll
+    for (int d = 0; d < ND; ++d) trunc[(size_t)i * NV + 1 + d] -= nt * n[d];
+  }
   // remove normal momentum of Solution_Old
   double vp = 0.0;
 #pragma unroll
@@ -230,6 +237,15 @@ __global__ void k_bc_heatflux_wall(int nV, int Pd, double wall_heat_flux, const 
   for (int r = 1; r <= ND; ++r) D[r * NV + r] = 1.0;
 }
 
+// momentum components of a [P][nDim+2] array := 0 at the vertices of a marker
+__global__ void k_zero_velocity(int nV, int Pd, int nDim, const int* __restrict__ vnode, double* __restrict__ arr) {
+  const int t = blockIdx.x * blockDim.x + threadIdx.x;
+  if (t >= nV) return;
+  const int i = vnode[t];
+  if (i >= Pd) return;
+  for (int d = 0; d < nDim; ++d) arr[(size_t)i * (nDim + 2) + 1 + d] = 0.0;
+}
+
 void flow_bc_far_field(su2b200_ctx* c, int iMarker) {
   ++c->sys[0].A_gen;
   ProfScope prof_(c, PROF_BC);
@@ -270,9 +286,9 @@ void flow_bc_sym_plane(su2b200_ctx* c, int iMarker) {
   if (m.nVertex == 0) return;
   const int nb = nblk(m.nVertex, 64);
   if (g.nDim == 2)
-    SU2B_LAUNCH(c, k_bc_sym_plane<2>, nb, 64, m.nVertex, g.Pd, m.node.p, m.unit_sym.p, g.row_ptr.p, s.U_old.p, s.res.p, c->sys[0].A.p);
+    SU2B_LAUNCH(c, k_bc_sym_plane<2>, nb, 64, m.nVertex, g.Pd, m.node.p, m.unit_sym.p, g.row_ptr.p, s.U_old.p, s.res.p, c->sys[0].A.p, s.res_trunc.p);
   else
-    SU2B_LAUNCH(c, k_bc_sym_plane<3>, nb, 64, m.nVertex, g.Pd, m.node.p, m.unit_sym.p, g.row_ptr.p, s.U_old.p, s.res.p, c->sys[0].A.p);
+    SU2B_LAUNCH(c, k_bc_sym_plane<3>, nb, 64, m.nVertex, g.Pd, m.node.p, m.unit_sym.p, g.row_ptr.p, s.U_old.p, s.res.p, c->sys[0].A.p, s.res_trunc.p);
 }
 
 void flow_bc_heatflux_wall(su2b200_ctx* c, int iMarker) {
@@ -287,6 +303,8 @@ void flow_bc_heatflux_wall(su2b200_ctx* c, int iMarker) {
     SU2B_LAUNCH(c, k_bc_heatflux_wall<2>, nb, 64, m.nVertex, g.Pd, m.heat_flux, m.node.p, m.normal.p, g.row_ptr.p, g.dia_ptr.p, s.U_old.p, s.res.p, c->sys[0].A.p);
   else
     SU2B_LAUNCH(c, k_bc_heatflux_wall<3>, nb, 64, m.nVertex, g.Pd, m.heat_flux, m.node.p, m.normal.p, g.row_ptr.p, g.dia_ptr.p, s.U_old.p, s.res.p, c->sys[0].A.p);
+  if (s.res_trunc.p)  // SetVel_ResTruncError_Zero (CNSSolver.cpp:511): no forcing on the momentum of a no-slip wall
+    SU2B_LAUNCH(c, k_zero_velocity, nb, 64, m.nVertex, g.Pd, g.nDim, m.node.p, s.res_trunc.p);
 }
 
 }  // namespace su2b200

@@ -72,8 +72,9 @@ int su2b200_destroy(su2b200_ctx* c) {
   cudaEventDestroy(c->ev0);
   cudaEventDestroy(c->ev1);
   cudaStream_t s0 = c->stream, s1 = c->comm_stream;
+  const bool borrowed = c->stream_borrowed;
   delete c;
-  cudaStreamDestroy(s0);
+  if (!borrowed) cudaStreamDestroy(s0);
   cudaStreamDestroy(s1);
   API_END
 }
@@ -419,6 +420,7 @@ static bool locate_array(su2b200_ctx* c, int which, double** p, size_t* n) {
     case SU2B200_ARR_ILU: return set(c->sys[0].ilu);
     case SU2B200_ARR_INVM: return set(c->sys[0].invM);
     case SU2B200_ARR_UNDER_RELAX: return set(s.under_relax);
+    case SU2B200_ARR_RES_TRUNC: return set(s.res_trunc);
     case SU2B200_ARR_TURB_SOLUTION: return set(s.nu);
     case SU2B200_ARR_TURB_SOLUTION_OLD: return set(s.nu_old);
     case SU2B200_ARR_TURB_GRADIENT: return set(s.nu_grad);

@@ -34,7 +34,7 @@ static void flow_preprocessing(su2b200_ctx* c, bool output, unsigned long* nonph
   auto& s = c->fs;
   const auto& cfg = c->cfg;
   const bool center = cfg.conv_scheme == SU2B200_CONV_JST;
-  const bool muscl = cfg.muscl != 0;
+  const bool muscl = cfg.muscl != 0 && cfg.mg_level == 0;  // MUSCL only on MESH_0 (CEulerSolver.cpp:1662)
   const bool limiter = cfg.limiter != SU2B200_LIMITER_NONE;
   const int nd = c->geo.nDim;
   flow_primitives(c);
@@ -47,8 +47,10 @@ static void flow_preprocessing(su2b200_ctx* c, bool output, unsigned long* nonph
     flow_jst_preprocess(c);
     if (c->nranks > 1) {
       halo_exchange(c, s.lambda.p, 1);
-      halo_exchange(c, s.sensor.p, 1);
-      halo_exchange(c, s.und_lapl.p, s.nVar);
+      if (cfg.mg_level == 0) {
+        halo_exchange(c, s.sensor.p, 1);
+        halo_exchange(c, s.und_lapl.p, s.nVar);
+      }
     }
   }
   if (!output) {
@@ -297,6 +299,390 @@ int su2b200_iterate(su2b200_ctx* c, int nIter, su2b200_iter_report* reports) {
       rep.linsol_iter_turb = c->lin_iters[1];
       rep.linsol_res_turb = res;
     }
+    if (reports) reports[it] = rep;
+  }
+  SU2B_CUDA(cudaStreamSynchronize(c->stream));
+  API_END
+}
+
+// ---- f1. FAS multigrid: CMultiGridIntegration (SU2_CFD/src/integration/CMultiGridIntegration.cpp) -------------------
+// Every level is a context of its own (geometry of the agglomerated grid, its CFL, mg_level > 0 => first-order / Lax
+// scheme); the transfer operators below are gather kernels over the Children_CV lists of the coarse level, on the
+// finest level's stream. The agglomeration itself (CMultiGridGeometry) is host preprocessing outside the hot path: the
+// coarse grids arrive through su2b200_geometry_upload like any other grid.
+}  // extern "C"
+
+namespace {
+inline int nblk_(long n, int bs) { return (int)((n + bs - 1) / bs); }
+
+// CSolver::MultigridRestriction (CSolver.hpp:4343-4362): volume-weighted average of the children
+template <int NV>
+__global__ void k_mg_restrict(int Pc, const int* __restrict__ cptr, const int* __restrict__ child,
+                              const double* __restrict__ volF, const double* __restrict__ volC,
+                              const double* __restrict__ UF, double* __restrict__ UC) {
+  const int ic = blockIdx.x * blockDim.x + threadIdx.x;
+  if (ic >= Pc) return;
+  double acc[NV];
+#pragma unroll
+  for (int v = 0; v < NV; ++v) acc[v] = 0.0;
+  const double scale = 1 / volC[ic];
+  for (int k = cptr[ic]; k < cptr[ic + 1]; ++k) {
+    const int f = child[k];
+    const double w = volF[f] * scale;
+#pragma unroll
+    for (int v = 0; v < NV; ++v) acc[v] += w * UF[(size_t)f * NV + v];
+  }
+#pragma unroll
+  for (int v = 0; v < NV; ++v) UC[(size_t)ic * NV + v] = acc[v];
+}
+// SetForcing_Term, first loop (:516-531): trunc_c = sum over children of damp * fine residual
+template <int NV>
+__global__ void k_mg_sum_children(int Pc, double factor, const int* __restrict__ cptr, const int* __restrict__ child,
+                                  const double* __restrict__ resF, double* __restrict__ truncC) {
+  const int ic = blockIdx.x * blockDim.x + threadIdx.x;
+  if (ic >= Pc) return;
+  double acc[NV];
+#pragma unroll
+  for (int v = 0; v < NV; ++v) acc[v] = 0.0;
+  for (int k = cptr[ic]; k < cptr[ic + 1]; ++k) {
+    const int f = child[k];
+#pragma unroll
+    for (int v = 0; v < NV; ++v) acc[v] += factor * resF[(size_t)f * NV + v];
+  }
+#pragma unroll
+  for (int v = 0; v < NV; ++v) truncC[(size_t)ic * NV + v] = acc[v];
+}
+__global__ void k_mg_axpy(size_t n, double alpha, const double* __restrict__ x, double* __restrict__ y) {
+  for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (size_t)gridDim.x * blockDim.x) y[i] += alpha * x[i];
+}
+// GetProlongated_Correction, first loop (:319-342): Solution_Old_c = u_c - restriction(u_f), in the reference's order
+template <int NV>
+__global__ void k_mg_correction(int Pc, const int* __restrict__ cptr, const int* __restrict__ child,
+                                const double* __restrict__ volF, const double* __restrict__ volC,
+                                const double* __restrict__ UF, const double* __restrict__ UC, double* __restrict__ UoldC) {
+  const int ic = blockIdx.x * blockDim.x + threadIdx.x;
+  if (ic >= Pc) return;
+  double acc[NV];
+#pragma unroll
+  for (int v = 0; v < NV; ++v) acc[v] = 0.0;
+  const double areaParent = volC[ic];
+  for (int k = cptr[ic]; k < cptr[ic + 1]; ++k) {
+    const int f = child[k];
+    const double areaChild = volF[f];
+#pragma unroll
+    for (int v = 0; v < NV; ++v) acc[v] -= UF[(size_t)f * NV + v] * areaChild / areaParent;
+  }
+#pragma unroll
+  for (int v = 0; v < NV; ++v) UoldC[(size_t)ic * NV + v] = acc[v] + UC[(size_t)ic * NV + v];
+}
+// second loop (:370-377): the correction of a coarse point goes to each of its children (fine LinSysRes)
+template <int NV>
+__global__ void k_mg_prolong(int Pc, const int* __restrict__ cptr, const int* __restrict__ child,
+                             const double* __restrict__ UoldC, double* __restrict__ resF) {
+  const int ic = blockIdx.x * blockDim.x + threadIdx.x;
+  if (ic >= Pc) return;
+  for (int k = cptr[ic]; k < cptr[ic + 1]; ++k) {
+    const int f = child[k];
+#pragma unroll
+    for (int v = 0; v < NV; ++v) resF[(size_t)f * NV + v] = UoldC[(size_t)ic * NV + v];
+  }
+}
+// SmoothProlongated_Correction (:383-456): one Jacobi sweep res = (old + c * sum of neighbours) / (1 + c * nNeighbours)
+template <int NV>
+__global__ void k_mg_smooth(int P, double coeff, const int* __restrict__ nptr, const int* __restrict__ nbr,
+                            const double* __restrict__ old, const double* __restrict__ cur, double* __restrict__ out) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= P) return;
+  double sum[NV];
+#pragma unroll
+  for (int v = 0; v < NV; ++v) sum[v] = 0.0;
+  for (int k = nptr[i]; k < nptr[i + 1]; ++k) {
+    const int j = nbr[k];
+#pragma unroll
+    for (int v = 0; v < NV; ++v) sum[v] += cur[(size_t)j * NV + v];
+  }
+  const double factor = 1.0 / (1.0 + coeff * (double)(nptr[i + 1] - nptr[i]));
+#pragma unroll
+  for (int v = 0; v < NV; ++v) out[(size_t)i * NV + v] = (old[(size_t)i * NV + v] + coeff * sum[v]) * factor;
+}
+template <int NV>
+__global__ void k_mg_restore_vertices(int nV, const int* __restrict__ vnode, const double* __restrict__ old,
+                                      double* __restrict__ res) {
+  const int t = blockIdx.x * blockDim.x + threadIdx.x;
+  if (t >= nV) return;
+  const int i = vnode[t];
+#pragma unroll
+  for (int v = 0; v < NV; ++v) res[(size_t)i * NV + v] = old[(size_t)i * NV + v];
+}
+// SetProlongated_Correction (:458-484): u_f += damp * correction, a NaN correction counts as zero
+__global__ void k_mg_apply(size_t n, double factor, double* __restrict__ res, double* __restrict__ U) {
+  for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (size_t)gridDim.x * blockDim.x) {
+    double r = res[i];
+    if (r != r) { r = 0.0; res[i] = 0.0; }
+    U[i] += factor * r;
+  }
+}
+__global__ void k_mg_zero_velocity(int nV, int Pd, int nDim, const int* __restrict__ vnode, double* __restrict__ arr) {
+  const int t = blockIdx.x * blockDim.x + threadIdx.x;
+  if (t >= nV) return;
+  const int i = vnode[t];
+  if (i >= Pd) return;
+  for (int d = 0; d < nDim; ++d) arr[(size_t)i * (nDim + 2) + 1 + d] = 0.0;
+}
+
+void require_link(su2b200_ctx* fine, su2b200_ctx* coarse) {
+  if (!fine || !coarse) throw Error("null context");
+  SU2B_CUDA(cudaSetDevice(fine->device));
+  SU2B_REQUIRE(fine->fs.allocated && coarse->fs.allocated, "allocate both levels first");
+  SU2B_REQUIRE(coarse->mg_fine == fine && coarse->mg_child_ptr.n == (size_t)coarse->geo.P + 1,
+               "levels are not linked (su2b200_mg_link)");
+  SU2B_REQUIRE(fine->nranks == 1, "multigrid runs on a single rank for now");
+}
+// no-slip walls of the COARSE level: momentum components of `arr` := 0 (SetVelSolutionVector / SetVelocity_Old /
+// SetVel_ResTruncError_Zero with a zero vector)
+void zero_wall_velocity(su2b200_ctx* coarse, double* arr) {
+  auto& g = coarse->geo;
+  for (auto& m : g.markers)
+    if (m.kind == SU2B200_HEAT_FLUX && m.nVertex > 0)
+      SU2B_LAUNCH(coarse, k_mg_zero_velocity, nblk_(m.nVertex, 64), 64, m.nVertex, g.Pd, g.nDim, m.node.p, arr);
+}
+#define MG_NV(nd, K, ...)                        \
+  do {                                           \
+    if ((nd) == 2) K<4> __VA_ARGS__; else K<5> __VA_ARGS__; \
+  } while (0)
+
+void mg_set_restricted_solution(su2b200_ctx* fine, su2b200_ctx* coarse) {
+  require_link(fine, coarse);
+  auto &gf = fine->geo, &gc = coarse->geo;
+  const int nb = nblk_(gc.Pd, 128);
+  if (gf.nDim == 2) k_mg_restrict<4><<<nb, 128, 0, fine->stream>>>(gc.Pd, coarse->mg_child_ptr.p, coarse->mg_child.p, gf.volume.p, gc.volume.p, fine->fs.U.p, coarse->fs.U.p);
+  else k_mg_restrict<5><<<nb, 128, 0, fine->stream>>>(gc.Pd, coarse->mg_child_ptr.p, coarse->mg_child.p, gf.volume.p, gc.volume.p, fine->fs.U.p, coarse->fs.U.p);
+  fine->launches++;
+  SU2B_CUDA(cudaGetLastError());
+  zero_wall_velocity(coarse, coarse->fs.U.p);
+}
+void mg_set_residual_term(su2b200_ctx* c) {
+  SU2B_REQUIRE(c->fs.res_trunc.n == c->fs.res.n, "no multigrid forcing term on this level");
+  const size_t n = (size_t)c->geo.Pd * c->fs.nVar;
+  k_mg_axpy<<<nblk_((long)n, 256), 256, 0, c->stream>>>(n, 1.0, c->fs.res_trunc.p, c->fs.res.p);
+  c->launches++;
+  SU2B_CUDA(cudaGetLastError());
+}
+void mg_set_forcing_term(su2b200_ctx* fine, su2b200_ctx* coarse, double damp) {
+  require_link(fine, coarse);
+  auto& gc = coarse->geo;
+  const int nb = nblk_(gc.Pd, 128);
+  if (gc.nDim == 2) k_mg_sum_children<4><<<nb, 128, 0, fine->stream>>>(gc.Pd, damp, coarse->mg_child_ptr.p, coarse->mg_child.p, fine->fs.res.p, coarse->fs.res_trunc.p);
+  else k_mg_sum_children<5><<<nb, 128, 0, fine->stream>>>(gc.Pd, damp, coarse->mg_child_ptr.p, coarse->mg_child.p, fine->fs.res.p, coarse->fs.res_trunc.p);
+  fine->launches++;
+  SU2B_CUDA(cudaGetLastError());
+  zero_wall_velocity(coarse, coarse->fs.res_trunc.p);
+  const size_t n = (size_t)gc.Pd * coarse->fs.nVar;
+  k_mg_axpy<<<nblk_((long)n, 256), 256, 0, fine->stream>>>(n, -1.0, coarse->fs.res.p, coarse->fs.res_trunc.p);
+  fine->launches++;
+  SU2B_CUDA(cudaGetLastError());
+}
+void mg_get_prolongated_correction(su2b200_ctx* fine, su2b200_ctx* coarse) {
+  require_link(fine, coarse);
+  auto &gf = fine->geo, &gc = coarse->geo;
+  const int nb = nblk_(gc.Pd, 128);
+  if (gc.nDim == 2) k_mg_correction<4><<<nb, 128, 0, fine->stream>>>(gc.Pd, coarse->mg_child_ptr.p, coarse->mg_child.p, gf.volume.p, gc.volume.p, fine->fs.U.p, coarse->fs.U.p, coarse->fs.U_old.p);
+  else k_mg_correction<5><<<nb, 128, 0, fine->stream>>>(gc.Pd, coarse->mg_child_ptr.p, coarse->mg_child.p, gf.volume.p, gc.volume.p, fine->fs.U.p, coarse->fs.U.p, coarse->fs.U_old.p);
+  fine->launches++;
+  SU2B_CUDA(cudaGetLastError());
+  zero_wall_velocity(coarse, coarse->fs.U_old.p);
+  if (gc.nDim == 2) k_mg_prolong<4><<<nb, 128, 0, fine->stream>>>(gc.Pd, coarse->mg_child_ptr.p, coarse->mg_child.p, coarse->fs.U_old.p, fine->fs.res.p);
+  else k_mg_prolong<5><<<nb, 128, 0, fine->stream>>>(gc.Pd, coarse->mg_child_ptr.p, coarse->mg_child.p, coarse->fs.U_old.p, fine->fs.res.p);
+  fine->launches++;
+  SU2B_CUDA(cudaGetLastError());
+}
+void mg_smooth_prolongated_correction(su2b200_ctx* c, int nSmooth, double coeff) {
+  if (nSmooth <= 0) return;
+  auto& g = c->geo;
+  auto& s = c->fs;
+  const size_t n = s.res.n;
+  dvec<double>& old = c->sys[0].vec(0);   // Residual_Old
+  dvec<double>& tmp = c->sys[0].vec(1);
+  SU2B_CUDA(cudaMemcpyAsync(old.p, s.res.p, n * sizeof(double), cudaMemcpyDeviceToDevice, c->stream));
+  for (int it = 0; it < nSmooth; ++it) {
+    if (g.nDim == 2) k_mg_smooth<4><<<nblk_(g.P, 128), 128, 0, c->stream>>>(g.P, coeff, g.nbr_ptr.p, g.nbr_pt.p, old.p, s.res.p, tmp.p);
+    else k_mg_smooth<5><<<nblk_(g.P, 128), 128, 0, c->stream>>>(g.P, coeff, g.nbr_ptr.p, g.nbr_pt.p, old.p, s.res.p, tmp.p);
+    c->launches++;
+    SU2B_CUDA(cudaGetLastError());
+    SU2B_CUDA(cudaMemcpyAsync(s.res.p, tmp.p, n * sizeof(double), cudaMemcpyDeviceToDevice, c->stream));
+    for (auto& m : g.markers) {  // boundary points keep the unsmoothed correction
+      if (m.nVertex == 0 || m.kind == SU2B200_SEND_RECEIVE) continue;
+      if (g.nDim == 2) k_mg_restore_vertices<4><<<nblk_(m.nVertex, 64), 64, 0, c->stream>>>(m.nVertex, m.node.p, old.p, s.res.p);
+      else k_mg_restore_vertices<5><<<nblk_(m.nVertex, 64), 64, 0, c->stream>>>(m.nVertex, m.node.p, old.p, s.res.p);
+      c->launches++;
+    }
+  }
+}
+void mg_set_prolongated_correction(su2b200_ctx* c, double damp) {
+  const size_t n = (size_t)c->geo.Pd * c->fs.nVar;
+  k_mg_apply<<<nblk_((long)n, 256), 256, 0, c->stream>>>(n, damp, c->fs.res.p, c->fs.U.p);
+  c->launches++;
+  SU2B_CUDA(cudaGetLastError());
+}
+
+// one smoothing step on a level == the body of MultiGrid_Cycle's pre/post-smoothing loops (:168-206) for EULER_IMPLICIT
+void mg_smooth_level(su2b200_ctx* c, double* rms, unsigned long* np, unsigned long* ne) {
+  auto& s = c->fs;
+  flow_preprocessing(c, false, np);
+  vec_copy(c, s.U.n, s.U.p, s.U_old.p);
+  flow_time_step(c);
+  flow_space_integration(c, ne);
+  flow_prepare_implicit(c, rms, nullptr, nullptr);
+  flow_linear_solve(c);
+  flow_complete_implicit(c);
+}
+
+// MultiGrid_Cycle (:129-300), recursion over the levels
+void mg_cycle(su2b200_ctx** lv, const su2b200_mg_config& mc, int iMesh, int recursive, double* rms_fine,
+              unsigned long* np, unsigned long* ne) {
+  su2b200_ctx* fine = lv[iMesh];
+  double rms[5] = {0, 0, 0, 0, 0};
+  for (int k = 0; k < mc.pre_smooth[iMesh]; ++k) {
+    mg_smooth_level(fine, rms, iMesh == 0 ? np : nullptr, iMesh == 0 ? ne : nullptr);
+    if (iMesh == 0) for (int v = 0; v < 5; ++v) rms_fine[v] = rms[v];
+  }
+  if (iMesh < mc.nLevels) {
+    su2b200_ctx* coarse = lv[iMesh + 1];
+    // r_k = P_k + F_k(u_k)   (the reference switches to EULER_EXPLICIT here only to skip the Jacobian)
+    flow_preprocessing(fine, false, nullptr);
+    flow_space_integration(fine, nullptr);
+    if (iMesh > 0) mg_set_residual_term(fine);  // the finest level carries no forcing term
+    // r_(k+1) = F_(k+1)(I u_k)
+    mg_set_restricted_solution(fine, coarse);
+    flow_preprocessing(coarse, false, nullptr);
+    flow_space_integration(coarse, nullptr);
+    // P_(k+1) = I(r_k) - r_(k+1)
+    mg_set_forcing_term(fine, coarse, mc.damp_restriction);
+    for (int imu = 0; imu <= recursive; ++imu) {
+      int next = recursive;
+      if (iMesh == mc.nLevels - 2) next = 0;
+      mg_cycle(lv, mc, iMesh + 1, next, rms_fine, np, ne);
+    }
+    mg_get_prolongated_correction(fine, coarse);
+    mg_smooth_prolongated_correction(fine, mc.correction_smooth[iMesh], 1.25);
+    mg_set_prolongated_correction(fine, mc.damp_prolongation);
+    for (int k = 0; k < mc.post_smooth[iMesh]; ++k) {
+      mg_smooth_level(fine, rms, nullptr, nullptr);
+      if (iMesh == 0) for (int v = 0; v < 5; ++v) rms_fine[v] = rms[v];
+    }
+  }
+}
+}  // namespace
+
+extern "C" {
+
+int su2b200_mg_link(su2b200_ctx* fine, su2b200_ctx* coarse, const unsigned long* children_ptr,
+                    const unsigned long* children) {
+  API_BEGIN
+  if (!fine || !coarse) throw Error("null context");
+  SU2B_CUDA(cudaSetDevice(fine->device));
+  SU2B_REQUIRE(fine->device == coarse->device, "multigrid levels must live on one device");
+  SU2B_REQUIRE(fine->fs.allocated && coarse->fs.allocated, "allocate both levels first");
+  SU2B_REQUIRE(children_ptr && children, "null children arrays");
+  SU2B_REQUIRE(fine->geo.nDim == coarse->geo.nDim && fine->fs.nVar == coarse->fs.nVar, "levels differ in nDim / nVar");
+  const int Pc = coarse->geo.P;
+  std::vector<int> cp(Pc + 1), ch(children_ptr[Pc]);
+  for (int i = 0; i <= Pc; ++i) cp[i] = (int)children_ptr[i];
+  std::vector<char> seen(fine->geo.P, 0);
+  for (size_t k = 0; k < ch.size(); ++k) {
+    SU2B_REQUIRE(children[k] < (unsigned long)fine->geo.P, "child index outside the fine grid");
+    SU2B_REQUIRE(!seen[children[k]], "a fine point has two parents");
+    seen[children[k]] = 1;
+    ch[k] = (int)children[k];
+  }
+  SU2B_CUDA(cudaStreamSynchronize(coarse->stream));
+  SU2B_CUDA(cudaStreamSynchronize(fine->stream));
+  coarse->mg_child_ptr.upload(cp);
+  coarse->mg_child.upload(ch);
+  coarse->mg_fine = fine;
+  if (!coarse->stream_borrowed) {  // every level on the finest level's stream: the cycle is one ordered sequence
+    cudaStreamDestroy(coarse->stream);
+    coarse->stream_borrowed = true;
+  }
+  coarse->stream = fine->stream;
+  for (su2b200_ctx* c : {fine, coarse}) {
+    if (c->fs.res_trunc.n != c->fs.res.n) {
+      c->fs.res_trunc.alloc(c->fs.res.n);
+      c->fs.res_trunc.zero(fine->stream);
+    }
+  }
+  SU2B_CUDA(cudaStreamSynchronize(fine->stream));
+  API_END
+}
+
+int su2b200_mg_set_restricted_solution(su2b200_ctx* fine, su2b200_ctx* coarse) {
+  API_BEGIN
+  mg_set_restricted_solution(fine, coarse);
+  API_END
+}
+int su2b200_mg_set_residual_term(su2b200_ctx* c) {
+  API_BEGIN
+  require_flow(c);
+  mg_set_residual_term(c);
+  API_END
+}
+int su2b200_mg_set_forcing_term(su2b200_ctx* fine, su2b200_ctx* coarse, double damp_restriction) {
+  API_BEGIN
+  mg_set_forcing_term(fine, coarse, damp_restriction);
+  API_END
+}
+int su2b200_mg_get_prolongated_correction(su2b200_ctx* fine, su2b200_ctx* coarse) {
+  API_BEGIN
+  mg_get_prolongated_correction(fine, coarse);
+  API_END
+}
+int su2b200_mg_smooth_prolongated_correction(su2b200_ctx* c, int nSmooth, double coeff) {
+  API_BEGIN
+  require_flow(c);
+  mg_smooth_prolongated_correction(c, nSmooth, coeff);
+  API_END
+}
+int su2b200_mg_set_prolongated_correction(su2b200_ctx* c, double damp_prolongation) {
+  API_BEGIN
+  require_flow(c);
+  mg_set_prolongated_correction(c, damp_prolongation);
+  API_END
+}
+
+// CMultiGridIntegration::MultiGrid_Iteration (:37-127): nIter FAS cycles, then Preprocessing(Output) + forces on the finest grid
+int su2b200_mg_iterate(su2b200_ctx** levels, const su2b200_mg_config* mc, int nIter, su2b200_iter_report* reports) {
+  API_BEGIN
+  SU2B_REQUIRE(levels && mc, "null argument");
+  SU2B_REQUIRE(mc->nLevels >= 1 && mc->nLevels <= 7, "nLevels (coarse levels) must be in 1..7");
+  for (int l = 0; l <= mc->nLevels; ++l) {
+    require_flow(levels[l]);
+    SU2B_REQUIRE(levels[l]->cfg.mg_level == l, "level contexts must be configured with mg_level = their position");
+    SU2B_REQUIRE(!levels[l]->cfg.rans_sa, "multigrid drives the mean-flow system only");
+    if (l > 0) SU2B_REQUIRE(levels[l]->mg_fine == levels[l - 1], "levels are not linked in order (su2b200_mg_link)");
+  }
+  su2b200_ctx* c = levels[0];
+  const int nv = c->fs.nVar;
+  for (int it = 0; it < nIter; ++it) {
+    su2b200_iter_report rep{};
+    unsigned long np = 0, ne = 0;
+    double rms[5] = {0, 0, 0, 0, 0};
+    int recursive = mc->cycle;  // 0 = V, 1 = W (FULLMG starts as V)
+    if (recursive > 1) recursive = 0;
+    mg_cycle(levels, *mc, 0, recursive, rms, &np, &ne);
+    for (int v = 0; v < nv; ++v) {
+      if (rms[v] != rms[v]) throw Error("SU2 has diverged (NaN detected).");
+      if (std::log10(rms[v]) > 20.0) throw Error("SU2 has diverged (Residual > 10^20 detected).");
+    }
+    flow_preprocessing(c, true, nullptr);
+    double coeffs[9] = {0};
+    flow_forces(c, coeffs);
+    for (int v = 0; v < nv; ++v) rep.rms_flow[v] = rms[v];
+    rep.CL = coeffs[0];
+    rep.CD = coeffs[1];
+    rep.linsol_iter_flow = c->lin_iters[0];
+    rep.linsol_res_flow = c->lin_res[0];
+    rep.nonphysical_points = np;
+    rep.nonphysical_edges = ne;
     if (reports) reports[it] = rep;
   }
   SU2B_CUDA(cudaStreamSynchronize(c->stream));

@@ -21,7 +21,9 @@ struct FlowParams {
   double muscl_kappa;            // MUSCL_KAPPA_FLOW
   double prandtl_turb;
   double jst_k2, jst_k4, jst_fix;
+  double lax_k0;                 // LAX_SENSOR_COEFF
   int muscl, limiter, viscous, implicit;
+  int lax;                       // centred scheme of an agglomerated multigrid level: CLaxScheme instead of CJSTScheme
 };
 
 template <int N>

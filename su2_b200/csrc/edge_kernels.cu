@@ -419,6 +419,14 @@ __global__ void __launch_bounds__(EDGE_BLOCK, EDGE_MIN_BLOCKS) k_edge_jst(EdgeAr
     lambda = 4 * phi_i * phi_j / (phi_i + phi_j) * lambda;
   }
   const double ni = (double)a.nnbr[i], nj = (double)a.nnbr[j];
+  if (p.lax) {
+    // CLaxScheme::finalizeFlux (centered.hpp:474-530): first-order scalar dissipation on the coarse multigrid levels
+    const double dissip = p.lax_k0 * ND * (ni + nj) / (ni * nj) * lambda;
+#pragma unroll
+    for (int v = 0; v < NV; ++v) flux[v] += dissip * diffU[v];
+    scalar_dissipation_jacobian<ND>(Vi, p.gamma, p.jst_fix * dissip, jac_i);
+    scalar_dissipation_jacobian<ND>(Vj, p.gamma, -p.jst_fix * dissip, jac_j);
+  } else {
   const double sc2 = 3 * (ni + nj) / (ni * nj);
   const double sc4 = 0.25 * sc2 * sc2;
   const double si = a.sensor[i], sj = a.sensor[j];
@@ -433,6 +441,7 @@ __global__ void __launch_bounds__(EDGE_BLOCK, EDGE_MIN_BLOCKS) k_edge_jst(EdgeAr
   const double dissip_j = -p.jst_fix * (eps2 + eps4 * (nj + 1)) * lambda;
   scalar_dissipation_jacobian<ND>(Vi, p.gamma, dissip_i, jac_i);
   scalar_dissipation_jacobian<ND>(Vj, p.gamma, dissip_j, jac_j);
+  }
 
   if (VISC) {
     double vij[ND];
@@ -507,10 +516,14 @@ static FlowParams make_flow_params(const su2b200_flow_config& c) {
   p.jst_k2 = c.jst_kappa2;
   p.jst_k4 = c.jst_kappa4;
   p.jst_fix = c.cent_jac_fix_factor;
-  p.muscl = c.muscl;
-  p.limiter = (c.limiter != SU2B200_LIMITER_NONE);
+  // agglomerated multigrid levels: first order (MUSCL only on MESH_0, CEulerSolver.cpp:1662) and, for centred
+  // schemes, the Lax-Friedrichs dissipation (CNumericsSIMD.cpp:70)
+  p.muscl = c.muscl && c.mg_level == 0;
+  p.limiter = (c.limiter != SU2B200_LIMITER_NONE) && c.mg_level == 0;
   p.viscous = c.viscous;
   p.implicit = 1;
+  p.lax = c.mg_level > 0;
+  p.lax_k0 = c.lax_kappa1;
   return p;
 }
 FlowParams flow_params(const su2b200_ctx* c) { return make_flow_params(c->cfg); }

@@ -896,6 +896,13 @@ void flow_jst_preprocess(su2b200_ctx* c) {
   ProfScope prof_(c, PROF_JST_PRE);
   auto& g = c->geo;
   auto& s = c->fs;
+  if (c->cfg.mg_level > 0) {
+    // agglomerated levels: SetMax_Eigenvalue only; sensor and undivided Laplacian belong to JST on MESH_0
+    // (center_jst = ... && iMesh == MESH_0, CEulerSolver.cpp:1584)
+    if (g.nDim == 2) spectral_radius_impl<2>(c, 0, s.lambda.p, nullptr);
+    else spectral_radius_impl<3>(c, 0, s.lambda.p, nullptr);
+    return;
+  }
   if (g.nDim == 2) {
     spectral_radius_impl<2>(c, 0, s.lambda.p, nullptr);
     LAUNCH(c, k_jst_sensor_lapl<2>, nblk(g.Pd, 128), 128, g.Pd, g.nbr_ptr.p, g.nbr_pt.p, g.phys_bnd.p, s.U.p, s.V.p,
@@ -918,7 +925,7 @@ void flow_vorticity_strain(su2b200_ctx* c) {
 // generic prepare-implicit for a system with NV variables
 template <int NV>
 static void prepare_implicit_impl(su2b200_ctx* c, LinSys& ls, const double* dt, double* res, double* sol,
-                                  double* out_rms, double* out_max, unsigned long* out_idx) {
+                                  const double* trunc, double* out_rms, double* out_max, unsigned long* out_idx) {
   ++ls.A_gen;  // V/dt lands on the diagonal blocks
   auto& g = c->geo;
   auto& s = c->fs;
@@ -929,8 +936,8 @@ static void prepare_implicit_impl(su2b200_ctx* c, LinSys& ls, const double* dt, 
   double* part_max = s.red.p + (size_t)nb * NV;
   int* part_idx = reinterpret_cast<int*>(s.red.p + (size_t)2 * nb * NV);
   double* out = s.red.p + (size_t)3 * nb * NV;
-  LAUNCH(c, k_prepare_implicit<NV>, nb, 256, g.Pd, ls.dia_ptr, g.volume.p, dt, ls.A.p, res, (const double*)nullptr,
-         sol, part_rms, part_max, part_idx);
+  LAUNCH(c, k_prepare_implicit<NV>, nb, 256, g.Pd, ls.dia_ptr, g.volume.p, dt, ls.A.p, res, trunc, sol, part_rms,
+         part_max, part_idx);
   LAUNCH(c, k_residual_final<NV>, 1, 256, nb, part_rms, part_max, part_idx, out);
   const size_t b = (size_t)g.Pd * NV, e = (size_t)g.P * NV;
   if (e > b) LAUNCH(c, k_zero_range, nblk(e - b, 256), 256, res, sol, b, e);
@@ -966,14 +973,16 @@ static void prepare_implicit_impl(su2b200_ctx* c, LinSys& ls, const double* dt, 
 void flow_prepare_implicit(su2b200_ctx* c, double* rms, double* mx, unsigned long* idx) {
   ProfScope prof_(c, PROF_PREPARE);
   auto& s = c->fs;
-  if (c->geo.nDim == 2) prepare_implicit_impl<4>(c, c->sys[0], s.dt.p, s.res.p, s.sol.p, rms, mx, idx);
-  else prepare_implicit_impl<5>(c, c->sys[0], s.dt.p, s.res.p, s.sol.p, rms, mx, idx);
+  // rhs = -(R + Res_TruncError): the multigrid forcing term of a coarse level (null without multigrid)
+  const double* trunc = s.res_trunc.p;
+  if (c->geo.nDim == 2) prepare_implicit_impl<4>(c, c->sys[0], s.dt.p, s.res.p, s.sol.p, trunc, rms, mx, idx);
+  else prepare_implicit_impl<5>(c, c->sys[0], s.dt.p, s.res.p, s.sol.p, trunc, rms, mx, idx);
 }
 
 void turb_prepare_implicit_generic(su2b200_ctx* c, double* rms, double* mx, unsigned long* idx) {
   ProfScope prof_(c, PROF_PREPARE);
   auto& s = c->fs;
-  prepare_implicit_impl<1>(c, c->sys[1], s.turb_dt.p, s.turb_res.p, s.turb_sol.p, rms, mx, idx);
+  prepare_implicit_impl<1>(c, c->sys[1], s.turb_dt.p, s.turb_res.p, s.turb_sol.p, nullptr, rms, mx, idx);
 }
 
 void flow_complete_implicit(su2b200_ctx* c) {

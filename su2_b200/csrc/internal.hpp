@@ -237,6 +237,10 @@ struct su2b200_ctx {
   std::vector<int> p2p_ranks, p2p_send_ptr, p2p_recv_ptr;
   su2b200::dvec<int> p2p_send_idx, p2p_recv_idx;
   su2b200::dvec<double> p2p_send_buf, p2p_recv_buf;
+  // FAS multigrid: this context as a COARSE level (children = points of the next finer level, CPoint::Children_CV)
+  su2b200_ctx* mg_fine = nullptr;
+  su2b200::dvec<int> mg_child_ptr, mg_child;
+  bool stream_borrowed = false;  // a coarse level runs on the stream of the finest one
   // last linear solve info
   unsigned long lin_iters[2] = {0, 0};
   double lin_res[2] = {0, 0};

@@ -306,6 +306,77 @@ class FlowSolver:
         return b.value, a.value
 
 
+class MultiGrid:
+    """CMultiGridIntegration stand-in: a list of FlowSolver levels (0 = finest) linked by their Children_CV lists.
+
+    levels[k] must be configured with mg_level = k (and the CFL of that level, CConfig::GetCFL(iMesh)); children[k-1]
+    = (children_ptr, children) of level k.  Method names follow CMultiGridIntegration.cpp."""
+
+    def __init__(self, levels, children, cycle=1, pre_smooth=(1, 2, 3, 3), post_smooth=(0, 0, 0, 0),
+                 correction_smooth=(0, 0, 0, 0), damp_restriction=1.0, damp_prolongation=1.0):
+        self.lib = capi.load()
+        self.levels = list(levels)
+        assert len(children) == len(self.levels) - 1
+        self._keep = []
+        for k, (cp, ch) in enumerate(children):
+            cp, ch = as_ulong(cp), as_ulong(ch)
+            self._keep.append((cp, ch))
+            check(self.lib.su2b200_mg_link(self.levels[k].ctx, self.levels[k + 1].ctx, ptr_ul(cp), ptr_ul(ch)))
+        mc = capi.MgConfig()
+        mc.nLevels, mc.cycle = len(self.levels) - 1, int(cycle)
+        for k in range(len(self.levels)):
+            mc.pre_smooth[k] = int(pre_smooth[k])
+            mc.post_smooth[k] = int(post_smooth[k])
+            mc.correction_smooth[k] = int(correction_smooth[k])
+        mc.damp_restriction, mc.damp_prolongation = float(damp_restriction), float(damp_prolongation)
+        self.cfg = mc
+
+    def SetRestricted_Solution(self, k):
+        check(self.lib.su2b200_mg_set_restricted_solution(self.levels[k].ctx, self.levels[k + 1].ctx))
+
+    def SetResidual_Term(self, k):
+        check(self.lib.su2b200_mg_set_residual_term(self.levels[k].ctx))
+
+    def SetForcing_Term(self, k):
+        check(self.lib.su2b200_mg_set_forcing_term(self.levels[k].ctx, self.levels[k + 1].ctx,
+                                                   C.c_double(self.cfg.damp_restriction)))
+
+    def GetProlongated_Correction(self, k):
+        check(self.lib.su2b200_mg_get_prolongated_correction(self.levels[k].ctx, self.levels[k + 1].ctx))
+
+    def SmoothProlongated_Correction(self, k, coeff=1.25):
+        check(self.lib.su2b200_mg_smooth_prolongated_correction(self.levels[k].ctx, int(self.cfg.correction_smooth[k]),
+                                                               C.c_double(coeff)))
+
+    def SetProlongated_Correction(self, k):
+        check(self.lib.su2b200_mg_set_prolongated_correction(self.levels[k].ctx, C.c_double(self.cfg.damp_prolongation)))
+
+    def smooth(self, k):
+        """One implicit smoothing step on level k (the pre/post-smoothing body of MultiGrid_Cycle)."""
+        s = self.levels[k]
+        s.Preprocessing(False)
+        s.Set_OldSolution()
+        s.SetTime_Step()
+        s.Space_Integration()
+        rms, _, _ = s.PrepareImplicitIteration()
+        s.Solve()
+        s.CompleteImplicitIteration()
+        return rms
+
+    def iterate(self, n=1):
+        """n FAS cycles on the device (su2b200_mg_iterate)."""
+        reps = (capi.IterReport * n)()
+        ctxs = (C.c_void_p * len(self.levels))(*[s.ctx for s in self.levels])
+        check(self.lib.su2b200_mg_iterate(ctxs, C.byref(self.cfg), int(n), reps))
+        nv = self.levels[0].nVar
+        return [dict(rms_flow=np.array(r.rms_flow[:nv]), CL=r.CL, CD=r.CD, linsol_iter_flow=r.linsol_iter_flow,
+                     linsol_res_flow=r.linsol_res_flow) for r in reps]
+
+    def close(self):
+        for s in reversed(self.levels):
+            s.close()
+
+
 class LinearSystem:
     """CSysMatrix + CSysSolve stand-in with host-buffer entry points (HtD/DtH inside every call)."""
 
