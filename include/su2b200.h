@@ -137,6 +137,10 @@ int su2b200_marker_upload(su2b200_ctx* ctx, int iMarker, int kindBC, unsigned lo
                           const unsigned long* vertex_normal_neighbor, const double* sym_unit_normal,
                           int monitoring, double heat_flux);
 
+/* CFVMFlowSolverBase::CharacPrimVar of a marker (CFVMFlowSolverBase.hpp:176): the far-field state BC_Far_Field computed
+ * for every vertex, [nVertex][nDim+9]; the scalar solvers' far-field fluxes read it (CScalarSolver.inl:382-441) */
+int su2b200_marker_charac_download(su2b200_ctx* ctx, int iMarker, double* host);
+
 /* Halo tables of CGeometry::PreprocessP2PComms (CGeometry.cpp:139-332): neighbour ranks, cumulative
  * point counts and the local point lists for send/recv. */
 int su2b200_p2p_upload(su2b200_ctx* ctx, int nNeighborRanks, const int* neighbor_rank,
@@ -371,6 +375,25 @@ int su2b200_linsys_solve(su2b200_ctx* ctx, int which, int solver, int prec, doub
                          const double* b, double* x, unsigned long* iterations, double* residual);
 /* CSysVector::dot (CSysVector.hpp:335-366) over owned entries, on the device */
 int su2b200_vector_dot(su2b200_ctx* ctx, int which, const double* a, const double* b, double* result);
+
+/* ---- restart / solution files in the SU2 native formats ------------------------------------------
+ * binary ".dat" (CSU2BinaryFileWriter.cpp:39-94, CSolver::Read_SU2_Restart_Binary CSolver.cpp:2916) and CSV
+ * (CSolver::Read_SU2_Restart_ASCII :2754); columns x,y[,z],Density,Momentum_*,Energy[,Nu_Tilde]; rows by GLOBAL point index
+ * (global_index[nPoint] = CPoint::GlobalIndex, NULL = identity), so files are independent of RCM and partitioning.
+ * A restart written here is read by the reference (RESTART_SOL= YES) and vice versa. */
+/* COutput::SetResultFiles (RESTART / RESTART_ASCII): the owned points of this rank; in parallel every rank writes its rows
+ * into the one binary file (rank 0 the header), nPointGlobal = global point count (0 = single rank) */
+int su2b200_restart_write(su2b200_ctx* ctx, const char* path, int binary, const unsigned long* global_index,
+                          unsigned long nPointGlobal);
+/* CFVMFlowSolverBase::LoadRestart_impl (CFVMFlowSolverBase.inl:824-1008) + CTurbSASolver::LoadRestart: Solution, Solution_Old
+ * (and nu~) of every local point (halos included) from the file; the format is detected from the magic number */
+int su2b200_restart_read(su2b200_ctx* ctx, const char* path, const unsigned long* global_index);
+/* the same on host arrays (no GPU needed): solution [nPoint][nDim+2], turb [nPoint] when nTurb = 1 */
+int su2b200_restart_write_arrays(const char* path, int binary, int nDim, int nTurb, unsigned long nPoint,
+                                 const unsigned long* global_index, unsigned long nPointGlobal, const double* coord,
+                                 const double* solution, const double* turb, int write_header);
+int su2b200_restart_read_arrays(const char* path, int nDim, int nTurb, unsigned long nPoint,
+                                const unsigned long* global_index, double* solution, double* turb);
 
 /* ---- communication: CSolver::InitiateComms/CompleteComms (CSolver.cpp:1406-1697) ------------ */
 /* 128-byte ncclUniqueId: rank 0 creates it, the host side broadcasts it (MPI_Bcast / torch.distributed) */

@@ -124,7 +124,16 @@ class CB200FlowBackend {
     std::vector<double> dt(nPoint);
     B200_CHECK(su2b200_array_download(flowCtx, SU2B200_ARR_DELTA_TIME, dt.data()));
     for (unsigned long i = 0; i < nPoint; ++i) flow->GetNodes()->SetDelta_Time(i, dt[i]);
-    (void)nDim;
+    /*--- ... and their far-field fluxes from the characteristic state of the flow far-field BC ---*/
+    for (unsigned short m = 0; m < geometry->GetnMarker(); ++m) {
+      if (config->GetMarker_All_KindBC(m) != FAR_FIELD) continue;
+      const unsigned long nV = geometry->GetnVertex(m);
+      const unsigned short nPrim = nDim + 9;
+      std::vector<double> ch((size_t)nV * nPrim);
+      B200_CHECK(su2b200_marker_charac_download(flowCtx, m, ch.data()));
+      for (unsigned long v = 0; v < nV; ++v)
+        for (unsigned short k = 0; k < nPrim; ++k) flow->SetCharacPrimVar(m, v, k, ch[v * nPrim + k]);
+    }
     if (linRes) *linRes = res;
     return iters;
   }

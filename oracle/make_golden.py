@@ -201,7 +201,38 @@ def run_history(name, out_dir=None):
     return _save(name, slim, out_dir)
 
 
+RESTARTS = ("box_euler", "box_rans_sa")
+
+
+def run_restart(case, out_dir=None):
+    """Restart fixtures: the reference's own .dat / .csv restart files after 6 iterations of `case`, and the history of
+    the reference RESTARTED from them (3 iterations) -- tests/golden/restart/."""
+    out_dir = out_dir or os.path.join(ROOT, "tests", "golden", "restart")
+    os.makedirs(out_dir, exist_ok=True)
+    text = _case_text(case)
+    hist_opts = {"TABULAR_FORMAT": "CSV", "HISTORY_OUTPUT": "(ITER, RMS_RES, AERO_COEFF, LINSOL)", "HISTORY_WRT_FREQ_INNER": "1"}
+    a = cfg_with(text, dict(hist_opts, ITER="6", OUTPUT_FILES="(RESTART, RESTART_ASCII)", RESTART_FILENAME="restart_flow",
+                            CONV_FILENAME="hist_a"))
+    b = cfg_with(text, dict(hist_opts, ITER="3", RESTART_SOL="YES", SOLUTION_FILENAME="restart_flow", OUTPUT_FILES="NONE",
+                            CONV_FILENAME="hist_b"))
+    tmp = tempfile.mkdtemp(prefix="golden_")
+    try:
+        exe = os.path.join(HERE, "_ref", "SU2_CFD")
+        for name, cfg in (("a.cfg", a), ("b.cfg", b)):
+            open(os.path.join(tmp, name), "w").write(cfg)
+            subprocess.run([exe, "-t", "1", name], cwd=tmp, check=True, stdout=subprocess.DEVNULL)
+        for ext in ("dat", "csv"):
+            shutil.copy(os.path.join(tmp, "restart_flow." + ext), os.path.join(out_dir, "%s.%s" % (case, ext)))
+        hist = _history_from_csv(os.path.join(tmp, "hist_b.csv"))
+    finally:
+        shutil.rmtree(tmp, ignore_errors=True)
+    np.savez_compressed(os.path.join(out_dir, case + "_restarted_history.npz"), history=hist)
+    print(case, "restart fixtures ->", out_dir)
+
+
 def run(name, **kw):
+    if name.startswith("restart:"):
+        return run_restart(name[8:], **kw)
     if name in CASES:
         return run_case(name, **kw)
     if name in VARIANTS:
@@ -212,6 +243,6 @@ def run(name, **kw):
 
 
 if __name__ == "__main__":
-    names = sys.argv[1:] or list(CASES) + list(VARIANTS) + list(HISTORIES)
+    names = sys.argv[1:] or list(CASES) + list(VARIANTS) + list(HISTORIES) + ["restart:" + c for c in RESTARTS]
     for n in names:
         run(n)

@@ -93,7 +93,7 @@ ARR = dict(
 # every symbol include/su2b200.h declares (tests check that the library exports all of them)
 EXPORTED_SYMBOLS = [
     "su2b200_create", "su2b200_destroy", "su2b200_last_error", "su2b200_version", "su2b200_synchronize",
-    "su2b200_geometry_upload", "su2b200_marker_upload", "su2b200_p2p_upload", "su2b200_flow_configure",
+    "su2b200_geometry_upload", "su2b200_marker_upload", "su2b200_marker_charac_download", "su2b200_p2p_upload", "su2b200_flow_configure",
     "su2b200_flow_allocate", "su2b200_array_size", "su2b200_array_download", "su2b200_array_upload",
     "su2b200_edge_counter_download", "su2b200_flow_preprocessing", "su2b200_flow_set_old_solution",
     "su2b200_flow_set_time_step", "su2b200_flow_edge_residual", "su2b200_flow_bc_far_field",
@@ -107,7 +107,8 @@ EXPORTED_SYMBOLS = [
     "su2b200_linsys_build_preconditioner", "su2b200_linsys_apply_preconditioner", "su2b200_linsys_solve",
     "su2b200_vector_dot", "su2b200_mg_link", "su2b200_mg_set_restricted_solution", "su2b200_mg_set_residual_term",
     "su2b200_mg_set_forcing_term", "su2b200_mg_get_prolongated_correction", "su2b200_mg_smooth_prolongated_correction",
-    "su2b200_mg_set_prolongated_correction", "su2b200_mg_iterate", "su2b200_comm_unique_id", "su2b200_comm_init", "su2b200_halo_exchange",
+    "su2b200_mg_set_prolongated_correction", "su2b200_mg_iterate", "su2b200_restart_write", "su2b200_restart_read",
+    "su2b200_restart_write_arrays", "su2b200_restart_read_arrays", "su2b200_comm_unique_id", "su2b200_comm_init", "su2b200_halo_exchange",
     "su2b200_timer_start", "su2b200_timer_stop", "su2b200_launch_count", "su2b200_bench_edge_kernel",
     "su2b200_bench_spmv", "su2b200_bench_prec", "su2b200_struct_sizes",
     "su2b200_mesh_create_box", "su2b200_mesh_read_su2", "su2b200_mesh_write_su2", "su2b200_mesh_stretch", "su2b200_mesh_destroy", "su2b200_mesh_set_marker",

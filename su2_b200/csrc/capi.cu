@@ -266,6 +266,15 @@ int su2b200_marker_upload(su2b200_ctx* c, int iMarker, int kindBC, unsigned long
   API_END
 }
 
+int su2b200_marker_charac_download(su2b200_ctx* c, int iMarker, double* host) {
+  API_BEGIN
+  require_ctx(c);
+  SU2B_REQUIRE(iMarker >= 0 && iMarker < (int)c->geo.markers.size() && host, "marker index out of range");
+  SU2B_CUDA(cudaStreamSynchronize(c->stream));
+  c->geo.markers[iMarker].charac.download(host);
+  API_END
+}
+
 int su2b200_p2p_upload(su2b200_ctx* c, int n, const int* ranks, const int* send_ptr, const unsigned long* send_idx,
                        const int* recv_ptr, const unsigned long* recv_idx) {
   API_BEGIN

@@ -163,6 +163,18 @@ class FlowSolver:
         check(self.lib.su2b200_linsys_set_wide_threshold(self.ctx, int(which), int(sweep_rows), int(factor_rows),
                                                          int(factor_mode)))
 
+    # ---- restart files (SU2 native formats) -----------------------------------------------------------------
+    def write_restart(self, path, binary=True, global_index=None, n_global=0):
+        """COutput::SetResultFiles(RESTART / RESTART_ASCII) of the owned points (su2b200_restart_write)."""
+        gi = as_ulong(global_index) if global_index is not None else None
+        check(self.lib.su2b200_restart_write(self.ctx, str(path).encode(), int(bool(binary)), ptr_ul(gi),
+                                             C.c_ulong(int(n_global))))
+
+    def load_restart(self, path, global_index=None):
+        """CSolver::LoadRestart: Solution (+ nu~) from a .dat / .csv restart file (su2b200_restart_read)."""
+        gi = as_ulong(global_index) if global_index is not None else None
+        check(self.lib.su2b200_restart_read(self.ctx, str(path).encode(), ptr_ul(gi)))
+
     def edge_counter(self):
         out = np.empty(self.nEdge, dtype=np.int8)
         check(self.lib.su2b200_edge_counter_download(self.ctx, out.ctypes.data_as(C.POINTER(C.c_byte))))

@@ -236,3 +236,37 @@ def test_long_history_and_converged_coefficients(case):
     if gold["cfg_rans_sa"]:
         mt = np.array([r["rms_turb"] for r in reps])
         assert np.max(np.abs(np.log10(mt[1:]) - np.log10(hist[1:, 5]))) <= 0.02
+
+
+# ---- restart files ----------------------------------------------------------------------------------------
+@pytest.mark.parametrize("case", ["box_euler", "box_rans_sa"])
+def test_restart_from_a_reference_file_continues_like_the_reference(case, tmp_path):
+    """LoadRestart from the reference's own .dat / .csv file (written after 6 iterations), then 3 iterations: the history
+    of the reference restarted from the same file; and a restart written from the device reads back bit for bit."""
+    rdir = os.path.join(ROOT, "tests", "golden", "restart")
+    gold = _gold(case)
+    gid = np.asarray(gold["global_index"]).astype(np.int64)
+    ref = np.load(os.path.join(rdir, case + "_restarted_history.npz"))["history"]
+    for ext in ("dat", "csv"):
+        s = make_solver(gold)
+        s.load_restart(os.path.join(rdir, case + "." + ext), gid)
+        reps = s.iterate(3)
+        nv = s.nVar
+        for i, r in enumerate(reps):
+            assert np.allclose(r["rms_flow"], ref[i, :nv], rtol=2e-6), (ext, i, r["rms_flow"], ref[i, :nv])
+            assert r["linsol_iter_flow"] == int(ref[i, 8]), (ext, i, r["linsol_iter_flow"], ref[i, 8])
+            assert abs(r["CD"] - ref[i, 7]) <= 2e-6 * max(1e-3, abs(ref[i, 7]))
+            if gold["cfg_rans_sa"]:
+                assert abs(r["rms_turb"] - ref[i, 5]) <= 2e-6 * abs(ref[i, 5])
+        out = str(tmp_path / ("mine." + ext))
+        s.write_restart(out, binary=(ext == "dat"), global_index=gid[:s.nPointDomain])
+        sol = s.get("SOLUTION")
+        s.close()
+        s2 = make_solver(gold)
+        s2.load_restart(out, gid)
+        back = s2.get("SOLUTION")
+        s2.close()
+        if ext == "dat":
+            assert np.array_equal(back, sol)
+        else:
+            assert np.allclose(back, sol, rtol=1e-14, atol=0)
