@@ -70,6 +70,7 @@ enum {
   SU2B200_ARR_ILU = 15,          /* CSysMatrix::ILU_matrix         [nnz][nVar][nVar]    */
   SU2B200_ARR_INVM = 16,         /* CSysMatrix::invM               [Pd][nVar][nVar]     */
   SU2B200_ARR_UNDER_RELAX = 17,  /* CVariable::UnderRelaxation     [P]                  */
+  SU2B200_ARR_LOCAL_CFL = 19,    /* CVariable::LocalCFL            [P] (empty unless cfl_adapt)                         */
   SU2B200_ARR_RES_TRUNC = 18,    /* CVariable::Res_TruncError      [P][nVar] (multigrid forcing term; empty without) */
   SU2B200_ARR_TURB_SOLUTION = 20,/* CTurbSAVariable::Solution      [P][1]               */
   SU2B200_ARR_TURB_GRADIENT = 21,/* CScalarVariable::Gradient      [P][1][nDim]         */
@@ -234,6 +235,11 @@ typedef struct {
                                         the scalar solver is below 0.875 -- in a serial run that is
                                         nEdge / (512 ceil(nEdge/512)) (CGeometry.cpp:3826, graph_toolbox.hpp:661), so
                                         small meshes with an unlucky edge count get it. 1 / 0 = on / off, -1 = that rule */
+  /* CFL adaptation (CSolver::AdaptCFLNumber, CSolver.cpp:1707-1949) */
+  int cfl_adapt;                     /* CFL_ADAPT                                                                      */
+  double cfl_adapt_param[6];         /* CFL_ADAPT_PARAM: factor down, factor up, CFL min, CFL max, acceptable linear
+                                        tolerance (0.001), starting iteration (0)                                      */
+  unsigned long n_inner_iter;        /* ITER: the stagnation window is min(100, ITER - 1) iterations                    */
   /* FAS multigrid (CMultiGridIntegration): the level this context represents */
   int mg_level;                      /* 0 = finest grid; > 0: agglomerated level (no MUSCL, no JST sensor/Laplacian:
                                         CEulerSolver.cpp:1584-1586, :1662; centred schemes use CLaxScheme, CNumericsSIMD.cpp:70) */
@@ -282,6 +288,10 @@ int su2b200_flow_prepare_implicit(su2b200_ctx* ctx, double* rms, double* max, un
 int su2b200_flow_linear_solve(su2b200_ctx* ctx, unsigned long* iterations, double* residual);
 /* CFVMFlowSolverBase::CompleteImplicitIteration_impl (CFVMFlowSolverBase.hpp:983-1008) incl. under-relaxation */
 int su2b200_flow_complete_implicit(su2b200_ctx* ctx);
+/* CSolver::AdaptCFLNumber (CSolver.cpp:1707-1949): per-point CVariable::LocalCFL scaled down / up from the linear solver
+ * residuals, the under-relaxation factors of the last update and the nonlinear residual series (flip-flop / stall
+ * detection); su2b200_iterate calls it after the turbulence iteration when cfl_adapt is set. min/max/avg of the new CFL. */
+int su2b200_flow_adapt_cfl(su2b200_ctx* ctx, unsigned long inner_iter, double* cfl_min, double* cfl_max, double* cfl_avg);
 /* CFVMFlowSolverBase::Pressure_Forces (+Friction_Forces) on MARKER_MONITORING: CL, CD, CSF, CMx..z, CFx..z */
 int su2b200_flow_forces(su2b200_ctx* ctx, double* coeffs /*[9]: CL CD CSF CFx CFy CFz CMx CMy CMz*/);
 

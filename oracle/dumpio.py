@@ -100,6 +100,9 @@ def config_from_dump(d):
         ref_origin=list(d["cfg_ref_origin"]),
         # CScalarSolver::ReducerStrategy of the run that made the fixture (dumped by newer fixtures; else the rule applies)
         turb_reducer=int(d.get("cfg_turb_reducer", -1)))
+    if "cfg_cfl_adapt" in d:  # fixtures made since CFL adaptation exists
+        kw.update(cfl_adapt=int(d["cfg_cfl_adapt"]), n_inner_iter=int(d["cfg_n_inner_iter"]),
+                  cfl_adapt_param=[float(x) for x in d["cfg_cfl_adapt_param"]])
     if kw["rans_sa"]:
         # free-stream eddy viscosity of the CTurbSASolver constructor (CTurbSASolver.cpp:100-134)
         t = kw["temperature_inf"]

@@ -51,6 +51,10 @@ VARIANTS = {
     "naca0012_rfgmres": ("naca0012_roe", {"LINEAR_SOLVER": "RESTARTED_FGMRES", "LINEAR_SOLVER_ITER": "12",
                                           "LINEAR_SOLVER_RESTART_FREQUENCY": "4"}, 6),
     "naca0012_ls": ("naca0012_roe", {"NUM_METHOD_GRAD_RECON": "LEAST_SQUARES"}, 6),  # unweighted LS is a reconstruction-only option
+    # CFL adaptation (CSolver::AdaptCFLNumber) with the shipped QuickStart parameters, from CFL 10; 40 iterations ramp it up
+    "naca0012_cfl_adapt": ("naca0012_roe", {"CFL_NUMBER": "10.0", "CFL_ADAPT": "YES",
+                                            "CFL_ADAPT_PARAM": "( 0.5, 1.5, 5.0, 400.0 )", "LINEAR_SOLVER_ERROR": "1E-4",
+                                            "ITER": "40"}, 40),
 }
 # name -> (base case, {option: value}, nIter, threads)
 HISTORIES = {
@@ -63,7 +67,7 @@ MATRIX_KEYS = ("_jacobian", "_ilu", "_invM")
 KEEP_MATRICES = ("bc_jacobian", "_ilu", "_invM", "turb_bc_jacobian", "turb_src_jacobian", "turb_edge_jacobian", "turb_conv_jacobian")
 GEOMETRY_KEYS = ("edge_nodes", "edge_normal", "coord", "volume", "point_ptr", "point_nbr", "point_edge", "row_ptr",
                  "col_ind", "dia_ptr", "edge_ptr", "nNeighbor", "physical_boundary", "wall_distance", "global_index")
-VARIANT_KEEP = ("it0_linsyssol", "it0_post_solution", "it0_linsol_iter", "it0_linsol_res", "it0_sys_linsysres",
+VARIANT_KEEP = ("it0_local_cfl", "it0_linsyssol", "it0_post_solution", "it0_linsol_iter", "it0_linsol_res", "it0_sys_linsysres",
                 "it0_pre_grad_recon", "it0_pre_limiter", "it0_res_rms", "history", "nIter")
 
 

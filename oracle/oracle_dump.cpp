@@ -205,6 +205,13 @@ class Dumper : public CSinglezoneDriver {
     w.scalar("cfg_cent_jac_fix_factor", c->GetCent_Jac_Fix_Factor());
     w.scalar("cfg_cfl", c->GetCFL(MESH_0)); w.scalar("cfg_cfl_turb_ratio", c->GetCFLRedCoeff_Turb());
     w.scalar("cfg_max_delta_time", c->GetMax_DeltaTime());
+    w.iscalar("cfg_cfl_adapt", c->GetCFL_Adapt() == YES);
+    {
+      double ap[6];
+      for (int k = 0; k < 6; ++k) ap[k] = c->GetCFL_AdaptParam(k);
+      w.f64("cfg_cfl_adapt_param", {6}, ap);
+    }
+    w.iscalar("cfg_n_inner_iter", c->GetnInner_Iter());
     w.scalar("cfg_max_update_flow", c->GetMaxUpdateFractionFlow()); w.scalar("cfg_max_update_sa", c->GetMaxUpdateFractionSA());
     w.iscalar("cfg_linear_solver", (long)c->GetKind_Linear_Solver()); w.iscalar("cfg_linear_prec", (long)c->GetKind_Linear_Solver_Prec());
     w.scalar("cfg_linear_tol", c->GetLinear_Solver_Error()); w.iscalar("cfg_linear_iter", c->GetLinear_Solver_Iter());
@@ -526,6 +533,13 @@ class Dumper : public CSinglezoneDriver {
         rms_turb = turb->GetRes_RMS(0);
         turb_iter = turb->GetIterLinSolver();
         turb_linres = turb->GetResLinSolver();
+      }
+      // CFluidIteration::Iterate (CFluidIteration.cpp:131-137)
+      if (config->GetCFL_Adapt() == YES) flow->AdaptCFLNumber(geometry_container[ZONE_0][INST_0], solver_container[ZONE_0][INST_0], config);
+      if (D && config->GetCFL_Adapt() == YES) {
+        std::vector<double> lc(P);
+        for (unsigned long i = 0; i < P; ++i) lc[i] = flow->nodes->GetLocalCFL(i);
+        w.f64(pre + "local_cfl", {P}, lc.data());
       }
       // history row: rms[nVar] (5 slots), rms_turb, CL, CD, lin iters/res flow, lin iters/res turb
       for (unsigned v = 0; v < 5; ++v) hist.push_back(v < nVar ? flow->GetRes_RMS(v) : 0.0);

@@ -54,6 +54,7 @@ class FlowConfig(C.Structure):
         ("aoa_deg", C.c_double), ("aos_deg", C.c_double), ("ref_area", C.c_double), ("ref_length", C.c_double),
         ("ref_origin", C.c_double * 3),
         ("assembly", C.c_int), ("prec_partitions", C.c_int), ("turb_reducer", C.c_int),
+        ("cfl_adapt", C.c_int), ("cfl_adapt_param", C.c_double * 6), ("n_inner_iter", C.c_ulong),
         ("mg_level", C.c_int), ("lax_kappa1", C.c_double),
     ]
 
@@ -86,7 +87,7 @@ ASSEMBLY_GATHER, ASSEMBLY_COLORED = 0, 1
 ARR = dict(
     SOLUTION=0, SOLUTION_OLD=1, PRIMITIVE=2, GRAD_RECON=3, GRAD_PRIM=4, LIMITER=5, DELTA_TIME=6, LINSYSRES=7,
     LINSYSSOL=8, JACOBIAN=9, LAMBDA=10, SENSOR=11, UND_LAPL=12, MAX_LAMBDA_INV=13, MAX_LAMBDA_VISC=14, ILU=15,
-    INVM=16, UNDER_RELAX=17, RES_TRUNC=18, TURB_SOLUTION=20, TURB_GRADIENT=21, TURB_LINSYSRES=22, TURB_LINSYSSOL=23,
+    INVM=16, UNDER_RELAX=17, RES_TRUNC=18, LOCAL_CFL=19, TURB_SOLUTION=20, TURB_GRADIENT=21, TURB_LINSYSRES=22, TURB_LINSYSSOL=23,
     TURB_JACOBIAN=24, EDDY_VISC=25, VORTICITY=26, STRAIN_MAG=27, WALL_DIST=28, TURB_DELTA_TIME=29,
     TURB_SOLUTION_OLD=30)
 
@@ -99,7 +100,7 @@ EXPORTED_SYMBOLS = [
     "su2b200_flow_set_time_step", "su2b200_flow_edge_residual", "su2b200_flow_bc_far_field",
     "su2b200_flow_bc_sym_plane", "su2b200_flow_bc_heatflux_wall", "su2b200_flow_space_integration",
     "su2b200_flow_prepare_implicit", "su2b200_flow_linear_solve", "su2b200_flow_complete_implicit",
-    "su2b200_flow_forces", "su2b200_turb_preprocessing", "su2b200_turb_set_time_step",
+    "su2b200_flow_forces", "su2b200_flow_adapt_cfl", "su2b200_turb_preprocessing", "su2b200_turb_set_time_step",
     "su2b200_turb_space_integration", "su2b200_turb_prepare_implicit", "su2b200_turb_linear_solve",
     "su2b200_turb_complete_implicit", "su2b200_turb_postprocessing", "su2b200_iterate", "su2b200_linsys_create",
     "su2b200_linsys_set_partitions", "su2b200_linsys_set_schedule", "su2b200_linsys_set_wide_threshold",

@@ -26,7 +26,7 @@ _DEFAULTS = {
     "LINEAR_SOLVER_RESTART_FREQUENCY": "10", "MAX_UPDATE_FLOW": "0.2", "MAX_UPDATE_SA": "0.99",
     "TIME_DISCRE_FLOW": "EULER_IMPLICIT", "MGLEVEL": "0", "SA_OPTIONS": "NONE", "MESH_FORMAT": "SU2",
     "MESH_FILENAME": "mesh.su2", "MESH_BOX_SIZE": "33, 33, 33", "MESH_BOX_LENGTH": "1.0, 1.0, 1.0",
-    "MESH_BOX_OFFSET": "0.0, 0.0, 0.0", "ITER": "1",
+    "MESH_BOX_OFFSET": "0.0, 0.0, 0.0", "ITER": "1", "CFL_ADAPT": "NO", "CFL_ADAPT_PARAM": "",
 }
 _MARKER_KEYS = {"MARKER_EULER": capi.EULER_WALL, "MARKER_FAR": capi.FAR_FIELD, "MARKER_SYM": capi.SYMMETRY_PLANE,
                 "MARKER_HEATFLUX": capi.HEAT_FLUX}
@@ -151,7 +151,11 @@ def flow_config_from_cfg(opts, nDim):
     muscl = int(o["MUSCL_FLOW"].upper() == "YES")
     if conv == "JST":  # centred schemes neither reconstruct nor limit (CConfig::SetPostprocessing)
         muscl, lim = 0, capi.LIMITER_NONE
+    adapt = [0.1, 1.2, 10.0, 100.0, 0.001, 0.0]  # default_cfl_adapt (CConfig.cpp:1831-1836)
+    for k, x in enumerate(_list(o["CFL_ADAPT_PARAM"])[:6]):
+        adapt[k] = float(x)
     kw = dict(
+        cfl_adapt=int(o["CFL_ADAPT"].upper() == "YES"), cfl_adapt_param=adapt, n_inner_iter=int(o["ITER"]),
         gamma=gamma, gas_constant=R_nd, viscous=int(viscous), rans_sa=int(rans), sa_negative=int(sa_neg),
         mu_ref=mu_ref / visc_ref, mu_temperature_ref=mu_tref / t_ref, mu_sutherland=mu_s / t_ref,
         mu_constant=mu_ref / visc_ref, prandtl_lam=float(o["PRANDTL_LAM"]), prandtl_turb=float(o["PRANDTL_TURB"]),

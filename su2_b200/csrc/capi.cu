@@ -363,6 +363,16 @@ int su2b200_flow_allocate(su2b200_ctx* c) {
   alloc0(s.lam_inv, P);
   alloc0(s.lam_visc, P);
   alloc0(s.under_relax, P);
+  if (c->cfg.cfl_adapt) {  // CVariable::LocalCFL starts at CFL_NUMBER everywhere (CVariable ctor / CSolver::SetInitialCondition)
+    std::vector<double> lc(P, c->cfg.cfl);
+    s.local_cfl.upload(lc);
+  } else {
+    s.local_cfl.release();
+  }
+  s.adapt_series.clear();
+  s.adapt_counter = 0;
+  s.adapt_old_func = s.adapt_new_func = 0.0;
+  c->inner_iter = 0;
   alloc0(s.lambda, P);
   alloc0(s.sensor, P);
   alloc0(s.und_lapl, (size_t)P * nv);
@@ -430,6 +440,7 @@ static bool locate_array(su2b200_ctx* c, int which, double** p, size_t* n) {
     case SU2B200_ARR_INVM: return set(c->sys[0].invM);
     case SU2B200_ARR_UNDER_RELAX: return set(s.under_relax);
     case SU2B200_ARR_RES_TRUNC: return set(s.res_trunc);
+    case SU2B200_ARR_LOCAL_CFL: return set(s.local_cfl);
     case SU2B200_ARR_TURB_SOLUTION: return set(s.nu);
     case SU2B200_ARR_TURB_SOLUTION_OLD: return set(s.nu_old);
     case SU2B200_ARR_TURB_GRADIENT: return set(s.nu_grad);

@@ -168,7 +168,9 @@ int su2b200_flow_space_integration(su2b200_ctx* c) {
 int su2b200_flow_prepare_implicit(su2b200_ctx* c, double* rms, double* mx, unsigned long* idx) {
   API_BEGIN
   require_flow(c);
-  flow_prepare_implicit(c, rms, mx, idx);
+  double r[5] = {0, 0, 0, 0, 0};
+  flow_prepare_implicit(c, r, mx, idx);
+  for (int v = 0; v < c->fs.nVar; ++v) { c->fs.last_rms[v] = r[v]; if (rms) rms[v] = r[v]; }
   API_END
 }
 
@@ -218,7 +220,10 @@ int su2b200_turb_space_integration(su2b200_ctx* c) {
 int su2b200_turb_prepare_implicit(su2b200_ctx* c, double* rms, double* mx, unsigned long* idx) {
   API_BEGIN
   require_flow(c);
-  turb_prepare_implicit_generic(c, rms, mx, idx);
+  double r = 0.0;
+  turb_prepare_implicit_generic(c, &r, mx, idx);
+  c->fs.last_rms_turb = r;
+  if (rms) *rms = r;
   API_END
 }
 int su2b200_turb_linear_solve(su2b200_ctx* c, unsigned long* iterations, double* residual) {
@@ -298,10 +303,22 @@ int su2b200_iterate(su2b200_ctx* c, int nIter, su2b200_iter_report* reports) {
       rep.rms_turb = trms;
       rep.linsol_iter_turb = c->lin_iters[1];
       rep.linsol_res_turb = res;
+      s.last_rms_turb = trms;
     }
+    for (int v = 0; v < nv; ++v) s.last_rms[v] = rms[v];
+    // CFluidIteration::Iterate (CFluidIteration.cpp:131-137): CFL adaptation closes the iteration
+    if (c->cfg.cfl_adapt) flow_adapt_cfl(c, c->inner_iter, nullptr, nullptr, nullptr);
+    ++c->inner_iter;
     if (reports) reports[it] = rep;
   }
   SU2B_CUDA(cudaStreamSynchronize(c->stream));
+  API_END
+}
+
+int su2b200_flow_adapt_cfl(su2b200_ctx* c, unsigned long inner_iter, double* cfl_min, double* cfl_max, double* cfl_avg) {
+  API_BEGIN
+  require_flow(c);
+  flow_adapt_cfl(c, inner_iter, cfl_min, cfl_max, cfl_avg);
   API_END
 }
 

@@ -442,13 +442,14 @@ __global__ void k_lambda_bnd(int nV, int Pd, int viscous, double gamma, double p
 }
 
 // final dt + min/max block reduction (CFVMFlowSolverBase.hpp:497-532); out[0]=min, out[1]=max per block
-__global__ void k_delta_time(int Pd, int viscous, double cfl, double max_dt, const double* __restrict__ volume,
-                             const double* __restrict__ lam_inv, const double* __restrict__ lam_visc,
-                             double* __restrict__ dt, double* __restrict__ blk_minmax) {
+__global__ void k_delta_time(int Pd, int viscous, double cfl_all, const double* __restrict__ local_cfl, double max_dt,
+                             const double* __restrict__ volume, const double* __restrict__ lam_inv,
+                             const double* __restrict__ lam_visc, double* __restrict__ dt, double* __restrict__ blk_minmax) {
   const int i = blockIdx.x * blockDim.x + threadIdx.x;
   double mn = 1e30, mx = 0.0;
   if (i < Pd) {
     const double vol = volume[i];
+    const double cfl = local_cfl ? local_cfl[i] : cfl_all;  // CVariable::LocalCFL
     if (vol != 0.0) {
       double ldt = cfl * vol / lam_inv[i];
       if (viscous) {
@@ -883,13 +884,121 @@ void flow_time_step(su2b200_ctx* c) {
   else spectral_radius_impl<3>(c, visc, s.lam_inv.p, s.lam_visc.p);
   const int nb = nblk(g.Pd, 256);
   if (s.red.n < (size_t)2 * nb + 16) s.red.alloc((size_t)2 * nb + 16);
-  LAUNCH(c, k_delta_time, nb, 256, g.Pd, visc, c->cfg.cfl, c->cfg.max_delta_time, g.volume.p, s.lam_inv.p,
-         s.lam_visc.p, s.dt.p, s.red.p);
+  LAUNCH(c, k_delta_time, nb, 256, g.Pd, visc, c->cfg.cfl, (const double*)s.local_cfl.p, c->cfg.max_delta_time,
+         g.volume.p, s.lam_inv.p, s.lam_visc.p, s.dt.p, s.red.p);
   LAUNCH(c, k_minmax_final, 1, 256, nb, s.red.p, s.red.p + 2 * nb);
   SU2B_CUDA(cudaMemcpyAsync(s.h_red, s.red.p + 2 * nb, 2 * sizeof(double), cudaMemcpyDeviceToHost, c->stream));
   SU2B_CUDA(cudaStreamSynchronize(c->stream));
   c->min_dt = s.h_red[0];
   c->max_dt = s.h_red[1];
+}
+
+// CSolver::AdaptCFLNumber, the point loop (CSolver.cpp:1846-1915): blk = {min, max, sum} of the new CFL per block
+__global__ void k_adapt_cfl(int Pd, int reduce, int reset, int can_increase, double fdec, double finc, double cfl_min,
+                            double cfl_max, double mg_factor, const double* __restrict__ ur_flow,
+                            const double* __restrict__ ur_turb, double* __restrict__ local_cfl,
+                            double* __restrict__ blk) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  double mn = 1e30, mx = 0.0, sum = 0.0;
+  if (i < Pd) {
+    double CFL = local_cfl[i];
+    const double ur = fmin(ur_flow[i], ur_turb ? ur_turb[i] : 1.0);
+    double factor;
+    if (ur < 0.1 || reduce) factor = fdec;
+    else if ((ur >= 0.1 && ur < 1.0) || !can_increase) factor = 1.0;
+    else factor = finc;
+    if (CFL * factor <= cfl_min) { CFL = cfl_min; factor = mg_factor; }
+    else if (CFL * factor >= cfl_max) { CFL = cfl_max; factor = mg_factor; }
+    if (reset) { CFL = cfl_min; factor = mg_factor; }
+    CFL *= factor;
+    local_cfl[i] = CFL;
+    mn = mx = sum = CFL;
+  }
+  __shared__ double smn[32], smx[32], ssm[32];
+  for (int o = 16; o > 0; o >>= 1) {
+    mn = fmin(mn, __shfl_xor_sync(0xffffffffu, mn, o));
+    mx = fmax(mx, __shfl_xor_sync(0xffffffffu, mx, o));
+    sum += __shfl_xor_sync(0xffffffffu, sum, o);
+  }
+  const int w = threadIdx.x >> 5, l = threadIdx.x & 31;
+  if (l == 0) { smn[w] = mn; smx[w] = mx; ssm[w] = sum; }
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    const int nw = blockDim.x >> 5;
+    for (int k = 1; k < nw; ++k) { mn = fmin(mn, smn[k]); mx = fmax(mx, smx[k]); sum += ssm[k]; }
+    blk[(size_t)blockIdx.x * 3 + 0] = mn;
+    blk[(size_t)blockIdx.x * 3 + 1] = mx;
+    blk[(size_t)blockIdx.x * 3 + 2] = sum;
+  }
+}
+
+// CSolver::AdaptCFLNumber (CSolver.cpp:1707-1949), finest grid: the decisions on the host from the linear residuals and
+// the nonlinear residual series of this context, the per-point update on the device
+void flow_adapt_cfl(su2b200_ctx* c, unsigned long inner_iter, double* out_min, double* out_max, double* out_avg) {
+  ProfScope prof_(c, PROF_UPDATE);
+  auto& g = c->geo;
+  auto& s = c->fs;
+  const auto& cfg = c->cfg;
+  SU2B_REQUIRE(s.local_cfl.n == (size_t)g.P, "CFL adaptation is off (su2b200_flow_config::cfl_adapt)");
+  const double fdec = cfg.cfl_adapt_param[0], finc = cfg.cfl_adapt_param[1], cmin = cfg.cfl_adapt_param[2],
+               cmax = cfg.cfl_adapt_param[3], acceptable = cfg.cfl_adapt_param[4], starting = cfg.cfl_adapt_param[5];
+  const unsigned long res_count = std::min(100ul, cfg.n_inner_iter > 0 ? cfg.n_inner_iter - 1 : 0ul);
+  const bool rans = cfg.rans_sa != 0;
+  const double linRes = std::max(c->lin_res[0], rans ? c->lin_res[1] : 0.0);
+  const double linTol = std::max(acceptable, cfg.linear_tol);
+  bool reset = linRes > 0.99;
+  bool reduce = (linRes > 1.2 * linTol) && ((double)inner_iter >= starting);
+  const bool can_increase = (linRes < linTol) && ((double)inner_iter >= starting);
+  if (res_count > 0) {
+    s.adapt_old_func = s.adapt_new_func;
+    if (s.adapt_series.empty()) s.adapt_series.assign(res_count, 0.0);
+    double f = 0.0;
+    int total = 0;
+    for (int v = 0; v < s.nVar; ++v) { f += std::log10(s.last_rms[v]); ++total; }
+    if (rans) { f += std::log10(s.last_rms_turb); ++total; }
+    s.adapt_new_func = f / total;
+    if (inner_iter == 1 && s.adapt_new_func - s.adapt_old_func > 10) s.adapt_old_func = s.adapt_new_func;
+    s.adapt_series[s.adapt_counter] = s.adapt_new_func - s.adapt_old_func;
+    if (++s.adapt_counter == res_count) s.adapt_counter = 0;
+    if (inner_iter >= res_count) {
+      unsigned long sign_changes = 0;
+      double total_change = 0.0;
+      double prev = s.adapt_series.front();
+      for (double val : s.adapt_series) {
+        total_change += val;
+        sign_changes += (prev > 0) ^ (val > 0);
+        prev = val;
+      }
+      reduce = reduce || ((sign_changes > res_count / 4) && (total_change > -0.5));
+      if (total_change > 2.0) {
+        reset = true;
+        s.adapt_counter = 0;
+        for (auto& val : s.adapt_series) val = 0.0;
+      }
+    }
+  }
+  const int nb = nblk(g.Pd, 256);
+  if (s.red.n < (size_t)3 * nb + 16) s.red.alloc((size_t)3 * nb + 16);
+  LAUNCH(c, k_adapt_cfl, nb, 256, g.Pd, (int)reduce, (int)reset, (int)can_increase, fdec, finc, cmin, cmax, 1.0,
+         (const double*)s.under_relax.p, rans ? (const double*)s.turb_under_relax.p : (const double*)nullptr,
+         s.local_cfl.p, s.red.p);
+  std::vector<double> blk((size_t)3 * nb);
+  SU2B_CUDA(cudaMemcpyAsync(blk.data(), s.red.p, blk.size() * sizeof(double), cudaMemcpyDeviceToHost, c->stream));
+  SU2B_CUDA(cudaStreamSynchronize(c->stream));
+  double v[3] = {1e30, 0.0, 0.0};
+  for (int b = 0; b < nb; ++b) { v[0] = std::min(v[0], blk[3 * b]); v[1] = std::max(v[1], blk[3 * b + 1]); v[2] += blk[3 * b + 2]; }
+  double npts = (double)g.Pd;
+  if (c->nranks > 1) {
+    allreduce_vec(c, &v[0], 1, 3);
+    allreduce_vec(c, &v[1], 1, 2);
+    double sums[2] = {v[2], npts};
+    allreduce_vec(c, sums, 2, 0);
+    v[2] = sums[0];
+    npts = sums[1];
+  }
+  if (out_min) *out_min = v[0];
+  if (out_max) *out_max = v[1];
+  if (out_avg) *out_avg = v[2] / npts;
 }
 
 void flow_jst_preprocess(su2b200_ctx* c) {

@@ -189,6 +189,12 @@ struct FlowState {
   dvec<double> lambda, sensor, und_lapl;     // JST
   dvec<double> res, sol;                     // LinSysRes, LinSysSol
   dvec<double> res_trunc;                    // Res_TruncError (zero without multigrid)
+  dvec<double> local_cfl;                    // CVariable::LocalCFL (CFL_ADAPT= YES only; else the scalar cfg.cfl)
+  // CSolver::AdaptCFLNumber bookkeeping (CSolver.hpp: Old_Func, New_Func, NonLinRes_Series, NonLinRes_Counter)
+  double adapt_old_func = 0.0, adapt_new_func = 0.0;
+  std::vector<double> adapt_series;
+  unsigned long adapt_counter = 0;
+  double last_rms[5] = {0, 0, 0, 0, 0}, last_rms_turb = 0.0;
   dvec<double> edge_flux;                    // SoA [nVar][E] (GATHER assembly)
   dvec<signed char> edge_counter;            // NonPhysicalEdgeCounter
   dvec<double> vorticity, strain_mag;
@@ -241,6 +247,7 @@ struct su2b200_ctx {
   su2b200_ctx* mg_fine = nullptr;
   su2b200::dvec<int> mg_child_ptr, mg_child;
   bool stream_borrowed = false;  // a coarse level runs on the stream of the finest one
+  unsigned long inner_iter = 0;  // CConfig::GetInnerIter of the next su2b200_iterate iteration
   // last linear solve info
   unsigned long lin_iters[2] = {0, 0};
   double lin_res[2] = {0, 0};

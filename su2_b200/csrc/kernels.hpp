@@ -15,6 +15,7 @@ void flow_vorticity_strain(su2b200_ctx* c);
 void flow_prepare_implicit(su2b200_ctx* c, double* rms, double* mx, unsigned long* idx);
 void turb_prepare_implicit_generic(su2b200_ctx* c, double* rms, double* mx, unsigned long* idx);
 void flow_complete_implicit(su2b200_ctx* c);
+void flow_adapt_cfl(su2b200_ctx* c, unsigned long inner_iter, double* cfl_min, double* cfl_max, double* cfl_avg);
 
 // edge_kernels.cu
 void flow_edge_residual(su2b200_ctx* c, unsigned long* nonphysical_edges);

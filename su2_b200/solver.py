@@ -91,7 +91,7 @@ class FlowSolver:
     def configure(self, **kw):
         cfg = default_config()
         for k, v in kw.items():
-            if k in ("velocity_inf", "ref_origin"):
+            if k in ("velocity_inf", "ref_origin", "cfl_adapt_param"):
                 arr = getattr(cfg, k)
                 for i, x in enumerate(v):
                     arr[i] = float(x)
@@ -482,4 +482,7 @@ def default_config():
     c.ref_area, c.ref_length = 1.0, 1.0
     c.assembly, c.prec_partitions = capi.ASSEMBLY_GATHER, 1
     c.turb_reducer, c.mg_level, c.lax_kappa1 = -1, 0, 0.15
+    c.cfl_adapt, c.n_inner_iter = 0, 1000
+    for k, v in enumerate((0.1, 1.2, 10.0, 100.0, 0.001, 0.0)):  # default_cfl_adapt (CConfig.cpp:1831-1836)
+        c.cfl_adapt_param[k] = v
     return c

@@ -270,3 +270,21 @@ def test_restart_from_a_reference_file_continues_like_the_reference(case, tmp_pa
             assert np.array_equal(back, sol)
         else:
             assert np.allclose(back, sol, rtol=1e-14, atol=0)
+
+
+def test_cfl_adaptation_follows_the_reference():
+    """CFL_ADAPT= YES (CSolver::AdaptCFLNumber): per-point LocalCFL after the first iteration equals the reference's, and
+    the 40-iteration history -- the CFL ramps from 10 where the update is not under-relaxed and the linear solver meets its
+    tolerance, and is cut where it does not -- follows the reference's (rms, CL/CD 1e-6, equal Krylov counts)."""
+    gold = _gold("naca0012_cfl_adapt")
+    s = make_solver(gold)
+    reps = s.iterate(1)
+    cfl = s.get("LOCAL_CFL")
+    ref = np.asarray(gold["it0_local_cfl"]).ravel()
+    assert np.array_equal(cfl[:s.nPointDomain], ref[:s.nPointDomain]), (np.unique(cfl), np.unique(ref))
+    reps += s.iterate(int(gold["nIter"]) - 1)
+    final = s.get("LOCAL_CFL")
+    s.close()
+    print("local CFL after %d iterations: min %.3g max %.3g" % (len(reps), final.min(), final.max()))
+    assert final.max() > 10.0
+    _check_history(reps, gold["history"], 4)
