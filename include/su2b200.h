@@ -165,6 +165,13 @@ int su2b200_mesh_write_su2(su2b200_mesh* mesh, const char* path);
 /* geometric stretching of a BOX/RECTANGLE mesh along `axis` before preprocessing: cell sizes first_cell, first_cell*ratio,
  * ... from the minus side, rescaled to the box length (the stretched wall-normal spacing of the "wing-box" input) */
 int su2b200_mesh_stretch(su2b200_mesh* mesh, int axis, double first_cell, double ratio);
+/* Decomposition of an undivided, not yet preprocessed mesh over nranks (SetColorGrid_Parallel + SetSendReceive,
+ * CPhysicalGeometry.cpp:7675-7755, :2956): point colouring by weighted recursive coordinate bisection with the reference's
+ * vertex weights (wp + we * degree), then per rank the owned points, the one-layer halo, every element touching an owned
+ * point, and the send / receive lists of CGeometry::PreprocessP2PComms. rank >= 0: that rank's local mesh;
+ * rank = -1: the whole mesh renumbered colour by colour, part_ptr[nranks+1] = first point of every colour (the row
+ * partitions with which one GPU reproduces the nranks-rank block-Jacobi preconditioner). Marker settings are inherited. */
+int su2b200_mesh_partition(su2b200_mesh* whole, int nranks, int rank, su2b200_mesh** out, unsigned long* part_ptr);
 int su2b200_mesh_destroy(su2b200_mesh* mesh);
 /* MARKER_EULER / MARKER_FAR / MARKER_SYM / MARKER_HEATFLUX + MARKER_MONITORING of the cfg file */
 int su2b200_mesh_set_marker(su2b200_mesh* mesh, const char* tag, int kindBC, int monitoring, double heat_flux);

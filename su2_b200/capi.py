@@ -112,7 +112,7 @@ EXPORTED_SYMBOLS = [
     "su2b200_restart_write_arrays", "su2b200_restart_read_arrays", "su2b200_comm_unique_id", "su2b200_comm_init", "su2b200_halo_exchange",
     "su2b200_timer_start", "su2b200_timer_stop", "su2b200_launch_count", "su2b200_bench_edge_kernel",
     "su2b200_bench_spmv", "su2b200_bench_prec", "su2b200_struct_sizes",
-    "su2b200_mesh_create_box", "su2b200_mesh_read_su2", "su2b200_mesh_write_su2", "su2b200_mesh_stretch", "su2b200_mesh_destroy", "su2b200_mesh_set_marker",
+    "su2b200_mesh_create_box", "su2b200_mesh_read_su2", "su2b200_mesh_write_su2", "su2b200_mesh_stretch", "su2b200_mesh_partition", "su2b200_mesh_destroy", "su2b200_mesh_set_marker",
     "su2b200_mesh_preprocess", "su2b200_mesh_sizes", "su2b200_mesh_array", "su2b200_mesh_marker_info",
     "su2b200_mesh_upload", "su2b200_profile_enable", "su2b200_profile_ncat", "su2b200_profile_name",
     "su2b200_profile_report",

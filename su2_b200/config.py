@@ -198,9 +198,12 @@ def mesh_from_cfg(opts, rank=0, nranks=1, base_dir=".", rcm=True, tets=False, st
         if stretch:
             m.stretch(*stretch)
     elif fmt == "SU2":
-        if nranks != 1:
-            raise ValueError("partitioned .su2 meshes are not supported yet (BOX/RECTANGLE only)")
         m = Mesh.read_su2(os.path.join(base_dir, o["MESH_FILENAME"]))
+        if nranks != 1:  # every rank reads the file and keeps its part (SetColorGrid_Parallel + SetSendReceive)
+            for tag, (kind, mon, q) in markers_from_cfg(o).items():
+                m.set_marker(tag, kind, mon, q)
+            whole, m = m, m.partition(nranks, rank)
+            whole.close()
     else:
         raise ValueError("MESH_FORMAT= %s not supported" % fmt)
     for tag, (kind, mon, q) in markers_from_cfg(o).items():

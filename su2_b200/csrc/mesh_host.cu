@@ -523,6 +523,183 @@ void rcm_reorder(su2b200_mesh& m) {
   else for (auto& p : m.perm) p = newIdx[p];
 }
 
+// ---- e2. decomposition of an unstructured mesh over N ranks --------------------------------------------------------------
+// The reference colours the points with ParMETIS k-way on the point graph, vertex weights wp + we * degree
+// (CPhysicalGeometry::SetColorGrid_Parallel, CPhysicalGeometry.cpp:7675-7755; PARMETIS_POINT_WEIGHT 0, PARMETIS_EDGE_WEIGHT 1)
+// and then builds, per rank, the owned points, a one-layer halo and the send/receive lists (SetSendReceive :2956,
+// PreprocessP2PComms CGeometry.cpp:139-332). ParMETIS is not part of this library; the colouring here is a weighted
+// recursive coordinate bisection with the SAME vertex weights (deterministic, balanced to one point's weight): any
+// colouring gives the same global answer, the partition only decides the halo volume. Everything after the colouring
+// follows the reference: a rank keeps every element that touches an owned point (so owned control volumes are
+// complete), owned points first, halos after them grouped by owner, both sides of a send/receive pair ordered by global
+// point index.
+void color_rcb(const su2b200_mesh& m, const std::vector<double>& w, std::vector<int>& idx, long b, long e, int c0, int nc,
+               std::vector<int>& color) {
+  if (nc == 1) {
+    for (long k = b; k < e; ++k) color[idx[k]] = c0;
+    return;
+  }
+  const int D = m.nDim;
+  double lo[3] = {1e300, 1e300, 1e300}, hi[3] = {-1e300, -1e300, -1e300};
+  for (long k = b; k < e; ++k)
+    for (int d = 0; d < D; ++d) {
+      const double x = m.coord[(size_t)idx[k] * D + d];
+      lo[d] = std::min(lo[d], x);
+      hi[d] = std::max(hi[d], x);
+    }
+  int axis = 0;
+  for (int d = 1; d < D; ++d)
+    if (hi[d] - lo[d] > hi[axis] - lo[axis]) axis = d;
+  std::stable_sort(idx.begin() + b, idx.begin() + e, [&](int p, int q) {
+    const double xp = m.coord[(size_t)p * D + axis], xq = m.coord[(size_t)q * D + axis];
+    return xp < xq || (xp == xq && p < q);
+  });
+  const int ncl = nc / 2;
+  double total = 0.0;
+  for (long k = b; k < e; ++k) total += w[idx[k]];
+  const double target = total * (double)ncl / (double)nc;
+  double acc = 0.0;
+  long cut = b;
+  while (cut < e && acc + 0.5 * w[idx[cut]] < target) acc += w[idx[cut++]];
+  cut = std::min(std::max(cut, b + 1), e - 1);
+  color_rcb(m, w, idx, b, cut, c0, ncl, color);
+  color_rcb(m, w, idx, cut, e, c0 + ncl, nc - ncl, color);
+}
+
+void color_points(const su2b200_mesh& m, int nranks, std::vector<int>& color) {
+  std::vector<long> ptr;
+  std::vector<int> nbr;
+  build_neighbours(m, ptr, nbr);
+  const double wp = 0.0, we = 1.0;  // PARMETIS_POINT_WEIGHT, PARMETIS_EDGE_WEIGHT defaults (CConfig.cpp:2944-2947)
+  std::vector<double> w(m.P);
+  for (long i = 0; i < m.P; ++i) w[i] = wp + we * (double)(ptr[i + 1] - ptr[i]);
+  std::vector<int> idx(m.P);
+  std::iota(idx.begin(), idx.end(), 0);
+  color.assign(m.P, 0);
+  color_rcb(m, w, idx, 0, m.P, 0, nranks, color);
+}
+
+// rank >= 0: the local mesh of that rank; rank == -1: the WHOLE mesh renumbered colour by colour (points of rank 0 first,
+// ... each group in ascending original index), the ordering in which one GPU reproduces the N-rank block-Jacobi
+// preconditioner with N row partitions (su2b200_linsys_set_partition_rows); part_ptr returns the group offsets
+su2b200_mesh* partition_mesh(const su2b200_mesh& whole, int nranks, int rank, std::vector<ulong_t>* part_ptr) {
+  SU2B_REQUIRE(whole.nranks == 1 && whole.P == whole.Pd, "partitioning starts from an undivided mesh");
+  SU2B_REQUIRE(!whole.preprocessed, "partition before preprocessing");
+  SU2B_REQUIRE(nranks >= 1 && rank >= -1 && rank < nranks, "invalid rank");
+  SU2B_REQUIRE(whole.P >= 2L * nranks, "too many ranks for this mesh");
+  std::vector<int> color;
+  color_points(whole, nranks, color);
+  const int D = whole.nDim;
+  auto* m = new su2b200_mesh();
+  m->nDim = D;
+  std::vector<int> local(whole.P, -1);  // new index of a point of the whole mesh (-1: not on this rank)
+  std::vector<int> pts;                 // points of the new mesh, in order (original indices)
+  if (rank < 0) {
+    if (part_ptr) part_ptr->assign(1, 0);
+    for (int c = 0; c < nranks; ++c) {
+      for (long i = 0; i < whole.P; ++i)
+        if (color[i] == c) { local[i] = (int)pts.size(); pts.push_back((int)i); }
+      if (part_ptr) part_ptr->push_back((ulong_t)pts.size());
+    }
+    m->Pd = whole.P;
+  } else {
+    m->rank = rank;
+    m->nranks = nranks;
+    for (long i = 0; i < whole.P; ++i)
+      if (color[i] == rank) { local[i] = (int)pts.size(); pts.push_back((int)i); }
+    m->Pd = (long)pts.size();
+    SU2B_REQUIRE(m->Pd > 0, "a rank received no points");
+    // halo layer: the other points of every element that touches an owned point, grouped by owner, ascending index
+    std::vector<char> halo(whole.P, 0);
+    for (long e = 0; e < whole.nElem(); ++e) {
+      bool touches = false;
+      for (long q = whole.eptr[e]; q < whole.eptr[e + 1]; ++q) touches = touches || color[whole.enode[q]] == rank;
+      if (!touches) continue;
+      for (long q = whole.eptr[e]; q < whole.eptr[e + 1]; ++q)
+        if (color[whole.enode[q]] != rank) halo[whole.enode[q]] = 1;
+    }
+    for (int c = 0; c < nranks; ++c) {
+      if (c == rank) continue;
+      const size_t before = pts.size();
+      for (long i = 0; i < whole.P; ++i)
+        if (halo[i] && color[i] == c) { local[i] = (int)pts.size(); pts.push_back((int)i); }
+      if (pts.size() > before) {
+        m->p2p_ranks.push_back(c);
+        for (size_t k = before; k < pts.size(); ++k) m->p2p_recv.push_back((ulong_t)k);
+        m->p2p_recv_ptr.push_back((int)m->p2p_recv.size());
+      }
+    }
+    // send lists: my owned points that are halos of rank c == share an element with a point owned by c. The halo
+    // relation is symmetric (an element with points of r and c makes halos on both sides), so the neighbour ranks
+    // found above are the complete list
+    std::vector<std::vector<char>> sendTo(m->p2p_ranks.size(), std::vector<char>());
+    std::vector<int> slot(nranks, -1);
+    for (size_t k = 0; k < m->p2p_ranks.size(); ++k) { slot[m->p2p_ranks[k]] = (int)k; sendTo[k].assign(whole.P, 0); }
+    for (long e = 0; e < whole.nElem(); ++e) {
+      unsigned long long mask = 0;  // owner ranks present in the element (as slots)
+      bool mine = false;
+      for (long q = whole.eptr[e]; q < whole.eptr[e + 1]; ++q) {
+        const int c = color[whole.enode[q]];
+        if (c == rank) mine = true;
+        else if (slot[c] >= 0 && slot[c] < 64) mask |= 1ull << slot[c];
+      }
+      if (!mine || !mask) continue;
+      for (long q = whole.eptr[e]; q < whole.eptr[e + 1]; ++q) {
+        const int p = whole.enode[q];
+        if (color[p] != rank) continue;
+        for (size_t k = 0; k < m->p2p_ranks.size(); ++k)
+          if (mask >> k & 1ull) sendTo[k][p] = 1;
+      }
+    }
+    SU2B_REQUIRE(m->p2p_ranks.size() <= 64, "more than 64 neighbour ranks");
+    for (size_t k = 0; k < m->p2p_ranks.size(); ++k) {
+      for (long i = 0; i < whole.P; ++i)
+        if (sendTo[k][i]) m->p2p_send.push_back((ulong_t)local[i]);
+      m->p2p_send_ptr.push_back((int)m->p2p_send.size());
+    }
+  }
+  m->P = (long)pts.size();
+  m->coord.resize((size_t)m->P * D);
+  m->global_index.resize(m->P);
+  for (long l = 0; l < m->P; ++l) {
+    for (int d = 0; d < D; ++d) m->coord[(size_t)l * D + d] = whole.coord[(size_t)pts[l] * D + d];
+    m->global_index[l] = whole.global_index[pts[l]];
+  }
+  auto keep = [&](const int* nd, int n) {
+    bool any = false;
+    for (int k = 0; k < n; ++k) {
+      if (local[nd[k]] < 0) return false;  // an element reaching beyond the halo layer (cannot touch an owned point)
+      any = any || local[nd[k]] < m->Pd;
+    }
+    return any;
+  };
+  for (long e = 0; e < whole.nElem(); ++e) {
+    const int n = (int)(whole.eptr[e + 1] - whole.eptr[e]);
+    const int* nd = &whole.enode[whole.eptr[e]];
+    if (!keep(nd, n)) continue;
+    int ln[8];
+    for (int k = 0; k < n; ++k) ln[k] = local[nd[k]];
+    add_elem(*m, whole.etype[e], ln, n);
+  }
+  for (const auto& wm : whole.markers) {
+    HostMarker mk;
+    mk.tag = wm.tag;
+    mk.kind = wm.kind;
+    mk.monitoring = wm.monitoring;
+    mk.heat_flux = wm.heat_flux;
+    for (size_t b = 0; b < wm.etype.size(); ++b) {
+      const int n = (int)(wm.eptr[b + 1] - wm.eptr[b]);
+      const int* nd = &wm.enode[wm.eptr[b]];
+      if (!keep(nd, n)) continue;
+      int ln[4];
+      for (int k = 0; k < n; ++k) ln[k] = local[nd[k]];
+      add_belem(mk, wm.etype[b], ln, n);
+    }
+    m->markers.push_back(std::move(mk));
+  }
+  return m;
+}
+
 bool is_sym_kind(int k) { return k == SU2B200_SYMMETRY_PLANE || k == SU2B200_EULER_WALL; }
 bool is_wall_kind(int k) { return k == SU2B200_HEAT_FLUX || k == 25 /*ISOTHERMAL*/; }
 
@@ -972,6 +1149,16 @@ int su2b200_mesh_stretch(su2b200_mesh* m, int axis, double first_cell, double ra
   API_BEGIN
   SU2B_REQUIRE(m, "null mesh");
   stretch_axis(*m, axis, first_cell, ratio);
+  API_END
+}
+
+int su2b200_mesh_partition(su2b200_mesh* whole, int nranks, int rank, su2b200_mesh** out, unsigned long* part_ptr) {
+  API_BEGIN
+  SU2B_REQUIRE(whole && out, "null argument");
+  std::vector<ulong_t> pp;
+  *out = partition_mesh(*whole, nranks, rank, &pp);
+  if (part_ptr && rank < 0)
+    for (size_t k = 0; k < pp.size(); ++k) part_ptr[k] = pp[k];
   API_END
 }
 

@@ -35,6 +35,15 @@ class Mesh:
         check(lib.su2b200_mesh_read_su2(str(path).encode(), C.byref(h)))
         return cls(h)
 
+    def partition(self, nranks, rank):
+        """Local mesh of `rank` out of `nranks` (su2b200_mesh_partition); rank = -1: the whole mesh renumbered colour by
+        colour, returned together with the first point of every colour."""
+        h = C.c_void_p()
+        pp = (C.c_ulong * (int(nranks) + 1))()
+        check(self.lib.su2b200_mesh_partition(self.h, int(nranks), int(rank), C.byref(h), pp))
+        m = Mesh(h)
+        return (m, [int(x) for x in pp]) if rank < 0 else m
+
     def write_su2(self, path):
         """ASCII .su2 file of the mesh in its current numbering (su2b200_mesh_write_su2)."""
         check(self.lib.su2b200_mesh_write_su2(self.h, str(path).encode()))

@@ -32,11 +32,38 @@ def _perturb(s, xyz, rans):
             s.set(name, s.get(name) * bump)
 
 
-def run_iterations(cfg_text, n_iter, rank, world, device, comm_id=None, partition_planes=None, overrides=None):
+def unstructured_mesh(opts, path, rank, world, nparts):
+    """Local part `rank` of `world` of the .su2 mesh at `path` (su2b200_mesh_partition), or -- world == 1 -- the whole mesh
+    renumbered colour by colour for `nparts` partitions.  Returns (preprocessed mesh, partition row offsets or None).
+    No RCM: the local order of a rank's owned points is then the order of its colour group in the renumbered whole."""
+    from .config import markers_from_cfg, _DEFAULTS
+    from .mesh import Mesh
+    o = dict(_DEFAULTS)
+    o.update(opts)
+    whole = Mesh.read_su2(path)
+    for tag, (kind, mon, q) in markers_from_cfg(o).items():
+        whole.set_marker(tag, kind, mon, q)
+    rows = None
+    if world > 1:
+        m = whole.partition(world, rank)
+    else:
+        m, rows = whole.partition(nparts, -1)
+    whole.close()
+    m.preprocess(rcm=False)
+    return m, rows
+
+
+def run_iterations(cfg_text, n_iter, rank, world, device, comm_id=None, partition_planes=None, overrides=None,
+                   su2_path=None, nparts=1):
     """`n_iter` iterations of the cfg's case on slab `rank` of `world` (or on the undivided mesh with the block-Jacobi
-    partitions given by `partition_planes` = cumulative plane counts).  Returns (global ids of the owned points, dict)."""
+    partitions given by `partition_planes` = cumulative plane counts).  With `su2_path` the mesh is that unstructured
+    file, decomposed by su2b200_mesh_partition.  Returns (global ids of the owned points, dict)."""
     opts = parse_cfg(cfg_text)
-    mesh = mesh_from_cfg(opts, rank=rank, nranks=world, rcm=False)
+    part_rows = None
+    if su2_path:
+        mesh, part_rows = unstructured_mesh(opts, su2_path, rank, world, nparts)
+    else:
+        mesh = mesh_from_cfg(opts, rank=rank, nranks=world, rcm=False)
     s = FlowSolver(device)
     try:
         if comm_id is not None:
@@ -45,8 +72,11 @@ def run_iterations(cfg_text, n_iter, rank, world, device, comm_id=None, partitio
         z = mesh.sizes()
         P, Pd = z["nPoint"], z["nPointDomain"]
         gid = mesh.array("global_index").astype(np.int64)
-        xyz = mesh.array("coord").reshape(P, 3)
-        kw = flow_config_from_cfg(opts, 3)
+        nd = z["nDim"]
+        xyz = mesh.array("coord").reshape(P, nd)
+        if nd == 2:
+            xyz = np.hstack([xyz, np.zeros((P, 1))])
+        kw = flow_config_from_cfg(opts, nd)
         kw.update(overrides or {})
         s.configure(**kw)
         s.allocate()
@@ -54,10 +84,11 @@ def run_iterations(cfg_text, n_iter, rank, world, device, comm_id=None, partitio
         rans = bool(kw["rans_sa"])
         if partition_planes is not None:
             plane = Pd // partition_planes[-1]
-            rows = [p * plane for p in partition_planes]
-            s.set_partition_rows(0, rows)
+            part_rows = [p * plane for p in partition_planes]
+        if part_rows is not None and len(part_rows) > 2:
+            s.set_partition_rows(0, part_rows)
             if rans:
-                s.set_partition_rows(1, rows)
+                s.set_partition_rows(1, part_rows)
         _perturb(s, xyz, rans)
         reps = s.iterate(n_iter)
         nv = s.nVar
@@ -109,14 +140,16 @@ def compare(parts, whole_gid, whole):
             "ok": bool(worst <= 1e-9 and rms_rel <= 1e-8 and iters_equal and coef("CL") <= 1e-6 and coef("CD") <= 1e-6)}
 
 
-def whole_iteration_parity(cfg_text, n_planes, n_iter, rank, world, device, comm_id, gather, overrides=None):
+def whole_iteration_parity(cfg_text, n_planes, n_iter, rank, world, device, comm_id, gather, overrides=None,
+                           su2_path=None):
     """Collective over the ranks: every rank runs its slab, rank 0 also runs the undivided mesh with `world` block-Jacobi
     partitions cut at the slab boundaries and compares.  `gather(obj)` returns the list of every rank's obj on rank 0
     (None elsewhere); `comm_id(solver)` returns the broadcast 128-byte NCCL id.  Returns the summary on rank 0."""
-    gid, mine = run_iterations(cfg_text, n_iter, rank, world, device, comm_id=comm_id, overrides=overrides)
+    gid, mine = run_iterations(cfg_text, n_iter, rank, world, device, comm_id=comm_id, overrides=overrides,
+                               su2_path=su2_path)
     parts = gather((gid, mine))
     if rank != 0:
         return None
-    gw, whole = run_iterations(cfg_text, n_iter, 0, 1, device, partition_planes=slab_planes(n_planes, world),
-                               overrides=overrides)
+    gw, whole = run_iterations(cfg_text, n_iter, 0, 1, device, overrides=overrides, su2_path=su2_path, nparts=world,
+                               partition_planes=None if su2_path else slab_planes(n_planes, world))
     return compare(parts, gw, whole)

@@ -275,3 +275,91 @@ def test_slab_decomposition_matches_the_undivided_mesh(nranks):
             assert np.all(rcv[rp_[rq]:rp_[rq + 1]] >= mq.sizes()["nPointDomain"])
     for m in parts + [whole]:
         m.close()
+
+
+def _partition_checks(make_whole, nranks):
+    """Unstructured decomposition (su2b200_mesh_partition): owned sets partition the points, owned control volumes are
+    complete, send and receive lists of a pair name the same global points in the same order, weights are balanced."""
+    whole = make_whole()
+    whole.preprocess(rcm=True)
+    wv = dict(zip(whole.array("global_index").astype(np.int64).tolist(), whole.array("volume").tolist()))
+    deg = dict(zip(whole.array("global_index").astype(np.int64).tolist(), np.diff(whole.array("point_ptr").astype(np.int64)).tolist()))
+    nE_whole = whole.sizes()["nEdge"]
+    parts = []
+    for r in range(nranks):
+        w = make_whole()
+        p = w.partition(nranks, r)
+        w.close()
+        p.preprocess(rcm=True)
+        parts.append(p)
+    owned, edges_owned = [], 0
+    for r, m in enumerate(parts):
+        z = m.sizes()
+        gid = m.array("global_index").astype(np.int64)
+        vol = m.array("volume")
+        Pd = z["nPointDomain"]
+        owned += gid[:Pd].tolist()
+        for g, v in zip(gid[:Pd], vol[:Pd]):
+            assert abs(v - wv[int(g)]) <= 1e-13 * abs(v), (r, g)
+        e0, e1 = m.array("edge_node0").astype(np.int64), m.array("edge_node1").astype(np.int64)
+        assert not np.any((e0 >= Pd) & (e1 >= Pd))  # no halo-halo edges
+        edges_owned += int(np.sum((e0 < Pd) & (e1 < Pd))) + 0.5 * int(np.sum((e0 < Pd) ^ (e1 < Pd)))
+    assert sorted(owned) == sorted(wv.keys())
+    assert edges_owned == nE_whole  # every edge once: interior edges on one rank, cut edges half on each side
+    sizes = [m.sizes()["nPointDomain"] for m in parts]
+    # balanced in the reference's vertex weight (wp + we * degree = the number of neighbours), to within a few points
+    load = [sum(deg[int(g)] for g in m.array("global_index").astype(np.int64)[:m.sizes()["nPointDomain"]]) for m in parts]
+    assert max(load) - min(load) <= 0.05 * sum(load) / nranks + 3 * max(deg.values()), load
+    for r, m in enumerate(parts):
+        ranks = m.array("p2p_ranks")
+        sp, snd = m.array("p2p_send_ptr"), m.array("p2p_send").astype(np.int64)
+        gid = m.array("global_index").astype(np.int64)
+        assert len(ranks) > 0
+        for k, q in enumerate(ranks):
+            mq = parts[int(q)]
+            rq = mq.array("p2p_ranks").tolist().index(r)
+            rp_, rcv = mq.array("p2p_recv_ptr"), mq.array("p2p_recv").astype(np.int64)
+            gq = mq.array("global_index").astype(np.int64)
+            mine, theirs = gid[snd[sp[k]:sp[k + 1]]], gq[rcv[rp_[rq]:rp_[rq + 1]]]
+            assert np.array_equal(mine, theirs) and len(mine) > 0
+            assert np.all(snd[sp[k]:sp[k + 1]] < m.sizes()["nPointDomain"])
+            assert np.all(rcv[rp_[rq]:rp_[rq + 1]] >= mq.sizes()["nPointDomain"])
+    # the whole mesh renumbered colour by colour: group sizes = the ranks' owned counts
+    w = make_whole()
+    ren, pp = w.partition(nranks, -1)
+    w.close()
+    assert [pp[k + 1] - pp[k] for k in range(nranks)] == sizes
+    ren.close()
+    for m in parts + [whole]:
+        m.close()
+
+
+@pytest.mark.parametrize("nranks", [2, 3, 4])
+def test_unstructured_partition_of_a_tetrahedral_box(nranks, tmp_path):
+    path = tmp_path / "tet.su2"
+    a = Mesh.box([7, 6, 5], [2.0, 1.0, 1.0], tets=True)
+    a.write_su2(path)
+    a.close()
+
+    def make():
+        m = Mesh.read_su2(path)
+        for t in ("x_minus", "x_plus", "y_minus", "y_plus", "z_minus", "z_plus"):
+            m.set_marker(t, capi.EULER_WALL if t.startswith("y") else capi.FAR_FIELD)
+        return m
+
+    _partition_checks(make, nranks)
+
+
+@pytest.mark.parametrize("nranks", [2, 4])
+def test_unstructured_partition_of_the_quickstart_mesh(nranks):
+    path = "/root/reference/QuickStart/mesh_NACA0012_inv.su2"
+    if not os.path.exists(path):
+        pytest.skip("QuickStart mesh not on this machine")
+
+    def make():
+        m = Mesh.read_su2(path)
+        m.set_marker("airfoil", capi.EULER_WALL, 1)
+        m.set_marker("farfield", capi.FAR_FIELD)
+        return m
+
+    _partition_checks(make, nranks)

@@ -71,7 +71,20 @@ def first_iteration(opts, rank, world, device, comm=None):
 def whole_iterations(kind, rank, world, local):
     from su2_b200.selfcheck import whole_iteration_parity
     n_planes = 6 * world + 1
+    su2_path = None
+    if kind.startswith("TET_"):
+        # unstructured path: a tetrahedral box written as .su2 by rank 0, decomposed by su2b200_mesh_partition
+        kind = kind[4:]
+        su2_path = "/tmp/su2b200_check_tet_%s.su2" % os.environ.get("MASTER_PORT", "0")
+        if rank == 0:
+            from su2_b200.mesh import Mesh
+            m = Mesh.box([11, 9, 8], [2.0, 1.0, 1.0], tets=True)
+            m.write_su2(su2_path)
+            m.close()
+        dist.barrier()
     text = bench.make_cfg(kind, [12, 10, n_planes], 1)
+    if su2_path:
+        text = text.replace("MESH_FORMAT= BOX", "MESH_FORMAT= SU2\nMESH_FILENAME= " + su2_path)
 
     def comm(s):
         idbuf = torch.zeros(128, dtype=torch.uint8, device="cuda")
@@ -85,7 +98,7 @@ def whole_iterations(kind, rank, world, local):
         dist.all_gather_object(parts, obj)
         return parts
 
-    res = whole_iteration_parity(text, n_planes, 5, rank, world, local, comm, gather)
+    res = whole_iteration_parity(text, n_planes, 5, rank, world, local, comm, gather, su2_path=su2_path)
     ok = 1.0
     if rank == 0:
         print("multigpu parity, whole iterations (%s, %d ranks): %s" % (kind, world, res))
