@@ -98,6 +98,7 @@ struct su2b200_mesh {
   std::vector<unsigned char> physical_boundary;
   std::vector<ulong_t> color_ptr, color_edges;
   std::vector<ulong_t> perm;  // new index of the point that had index i before reordering
+  std::vector<double> wall_distance_global;  // per ORIGINAL (global) point, set by the partitioner: the wall surface is global
   long nElem() const { return (long)etype.size(); }
 };
 
@@ -566,6 +567,9 @@ void color_rcb(const su2b200_mesh& m, const std::vector<double>& w, std::vector<
   color_rcb(m, w, idx, cut, e, c0 + ncl, nc - ncl, color);
 }
 
+void wall_distance(su2b200_mesh& m);  // below
+bool is_wall_kind(int k);
+
 void color_points(const su2b200_mesh& m, int nranks, std::vector<int>& color) {
   std::vector<long> ptr;
   std::vector<int> nbr;
@@ -697,6 +701,17 @@ su2b200_mesh* partition_mesh(const su2b200_mesh& whole, int nranks, int rank, st
     }
     m->markers.push_back(std::move(mk));
   }
+  // wall distance (RANS): the nearest wall element may lie on another rank -- computed once on the whole mesh
+  bool anyWall = false;
+  for (const auto& wm : whole.markers) anyWall = anyWall || is_wall_kind(wm.kind);
+  if (anyWall && !whole.is_box) {
+    su2b200_mesh tmp = whole;
+    wall_distance(tmp);
+    ulong_t maxg = 0;
+    for (long i = 0; i < whole.P; ++i) maxg = std::max(maxg, whole.global_index[i]);
+    m->wall_distance_global.assign(maxg + 1, 0.0);
+    for (long i = 0; i < whole.P; ++i) m->wall_distance_global[whole.global_index[i]] = tmp.wall_distance[i];
+  }
   return m;
 }
 
@@ -759,6 +774,10 @@ void wall_distance(su2b200_mesh& m) {
       }
       m.wall_distance[i] = best;
     }
+    return;
+  }
+  if (!m.wall_distance_global.empty()) {  // partitioned mesh: distances to the GLOBAL wall surface, by global index
+    for (long i = 0; i < m.P; ++i) m.wall_distance[i] = m.wall_distance_global[m.global_index[i]];
     return;
   }
   SU2B_REQUIRE(m.nranks == 1, "wall distance of a partitioned unstructured mesh needs the global wall surface");

@@ -284,6 +284,7 @@ def _partition_checks(make_whole, nranks):
     whole.preprocess(rcm=True)
     wv = dict(zip(whole.array("global_index").astype(np.int64).tolist(), whole.array("volume").tolist()))
     deg = dict(zip(whole.array("global_index").astype(np.int64).tolist(), np.diff(whole.array("point_ptr").astype(np.int64)).tolist()))
+    wd = dict(zip(whole.array("global_index").astype(np.int64).tolist(), whole.array("wall_distance").tolist()))
     nE_whole = whole.sizes()["nEdge"]
     parts = []
     for r in range(nranks):
@@ -301,6 +302,8 @@ def _partition_checks(make_whole, nranks):
         owned += gid[:Pd].tolist()
         for g, v in zip(gid[:Pd], vol[:Pd]):
             assert abs(v - wv[int(g)]) <= 1e-13 * abs(v), (r, g)
+        # the nearest wall may be on another rank: distances come from the global wall surface
+        assert np.array_equal(m.array("wall_distance"), np.array([wd[int(g)] for g in gid]))
         e0, e1 = m.array("edge_node0").astype(np.int64), m.array("edge_node1").astype(np.int64)
         assert not np.any((e0 >= Pd) & (e1 >= Pd))  # no halo-halo edges
         edges_owned += int(np.sum((e0 < Pd) & (e1 < Pd))) + 0.5 * int(np.sum((e0 < Pd) ^ (e1 < Pd)))
@@ -344,7 +347,7 @@ def test_unstructured_partition_of_a_tetrahedral_box(nranks, tmp_path):
     def make():
         m = Mesh.read_su2(path)
         for t in ("x_minus", "x_plus", "y_minus", "y_plus", "z_minus", "z_plus"):
-            m.set_marker(t, capi.EULER_WALL if t.startswith("y") else capi.FAR_FIELD)
+            m.set_marker(t, capi.HEAT_FLUX if t == "y_minus" else (capi.EULER_WALL if t == "y_plus" else capi.FAR_FIELD))
         return m
 
     _partition_checks(make, nranks)
