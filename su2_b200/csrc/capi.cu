@@ -71,6 +71,9 @@ int su2b200_destroy(su2b200_ctx* c) {
   if (c->fs.h_counters) cudaFreeHost(c->fs.h_counters);
   cudaEventDestroy(c->ev0);
   cudaEventDestroy(c->ev1);
+  if (c->ev_packed) cudaEventDestroy(c->ev_packed);
+  if (c->ev_unpacked) cudaEventDestroy(c->ev_unpacked);
+  if (c->comm_stream) cudaStreamSynchronize(c->comm_stream);
   cudaStream_t s0 = c->stream, s1 = c->comm_stream;
   const bool borrowed = c->stream_borrowed;
   delete c;
@@ -316,6 +319,7 @@ static void linsys_bind(su2b200_ctx* c, int which, int nVar) {
   ls.h_col_ind = g.h_col_ind;
   ls.h_dia_ptr = g.h_dia_ptr;
   ls.levels_ready = false;
+  ls.n_halo_rows = -1;
   ls.h_parts.clear();
   ls.A.alloc((size_t)g.nnz * nVar * nVar);
   ls.A.zero();

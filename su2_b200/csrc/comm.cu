@@ -91,6 +91,46 @@ void halo_exchange(su2b200_ctx* c, double* arr, int cnt) {
   SU2B_LAUNCH(c, k_unpack, nblk((long)nrecv * cnt, 256), 256, nrecv, cnt, c->p2p_recv_idx.p, c->p2p_recv_buf.p, arr);
 }
 
+// e3. The same exchange split in two so that interior work overlaps it: the pack runs on the compute stream (it reads what
+// the preceding kernel wrote), send/recv and the unpack run on comm_stream, and halo_exchange_finish makes the compute
+// stream wait for the unpack.  Between start and finish the compute stream may read the owned entries of `arr` and must
+// not trust (nor write) its halo entries.  One exchange in flight at a time (the staging buffers are shared).
+void halo_exchange_start(su2b200_ctx* c, double* arr, int cnt) {
+  if (c->nranks <= 1 || c->p2p_ranks.empty()) return;
+  SU2B_REQUIRE(c->nccl, "halo exchange requested without a communicator (su2b200_comm_init)");
+  SU2B_REQUIRE(!c->exchange_in_flight, "halo_exchange_start: the previous exchange was not finished");
+  if (!c->comm_stream) SU2B_CUDA(cudaStreamCreateWithFlags(&c->comm_stream, cudaStreamNonBlocking));
+  if (!c->ev_packed) {
+    SU2B_CUDA(cudaEventCreateWithFlags(&c->ev_packed, cudaEventDisableTiming));
+    SU2B_CUDA(cudaEventCreateWithFlags(&c->ev_unpacked, cudaEventDisableTiming));
+  }
+  const int nn = (int)c->p2p_ranks.size();
+  const int nsend = c->p2p_send_ptr[nn], nrecv = c->p2p_recv_ptr[nn];
+  if (c->p2p_send_buf.n < (size_t)nsend * cnt) c->p2p_send_buf.alloc((size_t)nsend * cnt);
+  if (c->p2p_recv_buf.n < (size_t)nrecv * cnt) c->p2p_recv_buf.alloc((size_t)nrecv * cnt);
+  SU2B_LAUNCH(c, k_pack, nblk((long)nsend * cnt, 256), 256, nsend, cnt, c->p2p_send_idx.p, arr, c->p2p_send_buf.p);
+  SU2B_CUDA(cudaEventRecord(c->ev_packed, c->stream));
+  SU2B_CUDA(cudaStreamWaitEvent(c->comm_stream, c->ev_packed, 0));
+  auto& api = nccl();
+  SU2B_NCCL(api.GroupStart());
+  for (int k = 0; k < nn; ++k) {
+    const int ns = c->p2p_send_ptr[k + 1] - c->p2p_send_ptr[k], nr = c->p2p_recv_ptr[k + 1] - c->p2p_recv_ptr[k];
+    if (nr) SU2B_NCCL(api.Recv(c->p2p_recv_buf.p + (size_t)c->p2p_recv_ptr[k] * cnt, (size_t)nr * cnt, 8, c->p2p_ranks[k], c->nccl, c->comm_stream));
+    if (ns) SU2B_NCCL(api.Send(c->p2p_send_buf.p + (size_t)c->p2p_send_ptr[k] * cnt, (size_t)ns * cnt, 8, c->p2p_ranks[k], c->nccl, c->comm_stream));
+  }
+  SU2B_NCCL(api.GroupEnd());
+  k_unpack<<<nblk((long)nrecv * cnt, 256), 256, 0, c->comm_stream>>>(nrecv, cnt, c->p2p_recv_idx.p, c->p2p_recv_buf.p, arr);
+  SU2B_CUDA(cudaGetLastError());
+  ++c->launches;
+  SU2B_CUDA(cudaEventRecord(c->ev_unpacked, c->comm_stream));
+  c->exchange_in_flight = true;
+}
+void halo_exchange_finish(su2b200_ctx* c) {
+  if (!c->exchange_in_flight) return;
+  SU2B_CUDA(cudaStreamWaitEvent(c->stream, c->ev_unpacked, 0));
+  c->exchange_in_flight = false;
+}
+
 // in-stream, in-place sum of n device doubles over the ranks (no host synchronisation)
 void allreduce_dev_sum(su2b200_ctx* c, double* d, int n) {
   if (c->nranks <= 1) return;

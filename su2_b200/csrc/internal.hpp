@@ -174,6 +174,9 @@ struct LinSys {
   dvec<double> scalars;              // device scalars for reductions
   double* h_scalars = nullptr;       // pinned host mirror
   double* h_mgs = nullptr;           // pinned: Hessenberg column of the device Gram-Schmidt
+  // owned rows with at least one halo column (multi-rank): redone by the overlapped product once the halos arrived
+  dvec<int> halo_rows;
+  int n_halo_rows = -1;              // -1: not built yet
   ~LinSys();
   dvec<double>& vec(size_t i);
   size_t vecLen() const { return (size_t)P * nVar; }
@@ -243,6 +246,10 @@ struct su2b200_ctx {
   std::vector<int> p2p_ranks, p2p_send_ptr, p2p_recv_ptr;
   su2b200::dvec<int> p2p_send_idx, p2p_recv_idx;
   su2b200::dvec<double> p2p_send_buf, p2p_recv_buf;
+  // overlapped exchange (e3): pack on the compute stream, send/recv + unpack on comm_stream, joined by events
+  cudaEvent_t ev_packed = nullptr, ev_unpacked = nullptr;
+  bool exchange_in_flight = false;
+  bool defer_halo = false;  // inside a Krylov solve: the operators skip their trailing exchange, the product does it overlapped
   // FAS multigrid: this context as a COARSE level (children = points of the next finer level, CPoint::Children_CV)
   su2b200_ctx* mg_fine = nullptr;
   su2b200::dvec<int> mg_child_ptr, mg_child;

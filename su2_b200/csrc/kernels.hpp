@@ -29,6 +29,7 @@ void flow_forces(su2b200_ctx* c, double* coeffs);
 // linalg.cu  (CSysMatrix / CSysVector)
 void linsys_bind_geometry(su2b200_ctx* c, int which, int nVar);
 void linsys_spmv(su2b200_ctx* c, LinSys& ls, const double* x, double* y);
+void linsys_spmv_exchange_x(su2b200_ctx* c, LinSys& ls, double* x, double* y);  // x: owned entries valid, halos exchanged here
 void linsys_build_jacobi(su2b200_ctx* c, LinSys& ls);
 void linsys_apply_jacobi(su2b200_ctx* c, LinSys& ls, const double* x, double* y);
 void linsys_build_ilu(su2b200_ctx* c, LinSys& ls);
@@ -60,6 +61,8 @@ void turb_postprocessing(su2b200_ctx* c);
 
 // comm.cu
 void halo_exchange(su2b200_ctx* c, double* arr, int count_per_point);
+void halo_exchange_start(su2b200_ctx* c, double* arr, int count_per_point);  // returns at once; the halos of arr are in flight
+void halo_exchange_finish(su2b200_ctx* c);                                   // the compute stream waits for them
 double allreduce_sum(su2b200_ctx* c, double v);
 void allreduce_dev_sum(su2b200_ctx* c, double* d, int n);       // device buffer, in stream
 void allreduce_vec(su2b200_ctx* c, double* v, int n, int op);  // op: 0 sum, 2 max, 3 min

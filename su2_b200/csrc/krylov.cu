@@ -244,7 +244,7 @@ static unsigned long fgmres(su2b200_ctx* c, LinSys& ls, int prec, double tol, in
   for (i = 0; i < m; i++) {
     if (beta < tol * norm0) break;
     linsys_apply_prec(c, ls, prec, V(i), Z(i));
-    linsys_spmv(c, ls, Z(i), V(i + 1));
+    linsys_spmv_exchange_x(c, ls, Z(i), V(i + 1));
     // ModGramSchmidt(i, H, V)
     {
       std::vector<double> hcol(i + 2, 0.0);
@@ -311,13 +311,13 @@ static unsigned long bcgstab(su2b200_ctx* c, LinSys& ls, int prec, double tol, i
     const double beta = (rho / rho_prime) * (alpha / omega);
     SU2B_LAUNCH(c, k_bcg_p, vgrid(n), 256, n, beta, omega, v, r, p);
     linsys_apply_prec(c, ls, prec, p, z);
-    linsys_spmv(c, ls, z, v);
+    linsys_spmv_exchange_x(c, ls, z, v);
     const double r_0_v = vec_dot(c, ls, r_0, v);
     alpha = rho / r_0_v;
     vec_axpy(c, n, alpha, z, x);
     vec_axpy(c, n, -alpha, v, r);
     linsys_apply_prec(c, ls, prec, r, z);
-    linsys_spmv(c, ls, z, A_x);
+    linsys_spmv_exchange_x(c, ls, z, A_x);
     omega = vec_dot(c, ls, A_x, A_x);
     if (omega == 0.0) break;
     omega = vec_dot(c, ls, A_x, r) / omega;
@@ -336,6 +336,14 @@ unsigned long linsys_solve(su2b200_ctx* c, LinSys& ls, int solver, int prec, dou
   linsys_build_prec(c, ls, prec);
   unsigned long it = 0;
   double res = 0.0;
+  // e3: inside the solve the preconditioners and products leave their trailing halo exchange to the overlapped product
+  // (SU2B200_OVERLAP=0: every operator exchanges its own output in-stream, as the reference's CSysMatrixComms does)
+  static const bool overlap = !(getenv("SU2B200_OVERLAP") && atoi(getenv("SU2B200_OVERLAP")) == 0);
+  struct DeferGuard {
+    su2b200_ctx* c;
+    ~DeferGuard() { c->defer_halo = false; }
+  } guard_{c};
+  c->defer_halo = overlap && c->nranks > 1;
   try {
   switch (solver) {
     case SU2B200_SOLVER_FGMRES:

@@ -262,7 +262,7 @@ void linsys_spmv(su2b200_ctx* c, LinSys& ls, const double* x, double* y) {
     if (ls.nVar == 4) SU2B_LAUNCH(c, k_spmv_rows<4>, nblk(warps * 32, 128), 128, ls.Pd, ls.row_ptr, ls.col_ind, ls.A.p, x, y);
     else if (ls.nVar == 5) SU2B_LAUNCH(c, k_spmv_rows<5>, nblk(warps * 32, 128), 128, ls.Pd, ls.row_ptr, ls.col_ind, ls.A.p, x, y);
     else throw Error("linsys_spmv: unsupported nVar");
-    if (c->nranks > 1) halo_exchange(c, y, ls.nVar);
+    if (c->nranks > 1 && !c->defer_halo) halo_exchange(c, y, ls.nVar);
     return;
   }
   switch (ls.nVar) {
@@ -271,7 +271,71 @@ void linsys_spmv(su2b200_ctx* c, LinSys& ls, const double* x, double* y) {
     case 5: SU2B_LAUNCH(c, k_spmv<5>, nblk(threads, 256), 256, ls.Pd, ls.row_ptr, ls.col_ind, ls.A.p, x, y); break;
     default: throw Error("linsys_spmv: unsupported nVar");
   }
-  if (c->nranks > 1) halo_exchange(c, y, ls.nVar);
+  if (c->nranks > 1 && !c->defer_halo) halo_exchange(c, y, ls.nVar);
+}
+
+// e3. Product of a Krylov iteration, y = A x with x fresh from the preconditioner (owned entries only): the halos of x travel
+// on comm_stream while EVERY owned row is multiplied; the rows with a halo column (a thin layer next to the rank
+// boundary) read stale halos in that pass and are multiplied again once the exchange has landed.  The halos of y are not
+// exchanged: no Krylov operation reads them (dots run over owned entries, the preconditioners over owned rows and columns).
+template <int NV>
+__global__ void __launch_bounds__(128) k_spmv_row_list(int n, const int* __restrict__ rows, const int* __restrict__ row_ptr,
+                                                       const int* __restrict__ col_ind, const double* __restrict__ A,
+                                                       const double* __restrict__ x, double* __restrict__ y) {
+  // one warp per listed row; lane = (k, r): block column k of the row (strided), block row r... kept simple: the list is
+  // a few per cent of the rows
+  const int w = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31;
+  if (w >= n) return;
+  const int row = rows[w];
+  const int kb = row_ptr[row], ke = row_ptr[row + 1];
+  constexpr int LPB = NV * NV;
+  double acc[NV];
+#pragma unroll
+  for (int r = 0; r < NV; ++r) acc[r] = 0.0;
+  for (int k = kb + lane; k < ke; k += 32) {
+    const int col = col_ind[k];
+#pragma unroll
+    for (int r = 0; r < NV; ++r)
+#pragma unroll
+      for (int cc = 0; cc < NV; ++cc) acc[r] += A[(size_t)k * LPB + r * NV + cc] * x[(size_t)col * NV + cc];
+  }
+#pragma unroll
+  for (int r = 0; r < NV; ++r) {
+    double v = acc[r];
+    for (int o = 16; o > 0; o >>= 1) v += __shfl_down_sync(FULL, v, o);
+    if (lane == 0) y[(size_t)row * NV + r] = v;
+  }
+}
+
+static void build_halo_rows(LinSys& ls) {
+  std::vector<int> rows;
+  for (int i = 0; i < ls.Pd; ++i)
+    for (int k = ls.h_row_ptr[i]; k < ls.h_row_ptr[i + 1]; ++k)
+      if (ls.h_col_ind[k] >= ls.Pd) { rows.push_back(i); break; }
+  ls.n_halo_rows = (int)rows.size();
+  if (!rows.empty()) ls.halo_rows.upload(rows);
+}
+
+void linsys_spmv_exchange_x(su2b200_ctx* c, LinSys& ls, double* x, double* y) {
+  if (c->nranks <= 1 || !c->defer_halo) {
+    // the operator that produced x has exchanged it already
+    linsys_spmv(c, ls, x, y);
+    return;
+  }
+  if (ls.n_halo_rows < 0) build_halo_rows(ls);
+  halo_exchange_start(c, x, ls.nVar);
+  linsys_spmv(c, ls, x, y);
+  halo_exchange_finish(c);
+  if (ls.n_halo_rows > 0) {
+    ProfScope prof_(c, PROF_SPMV);
+    const int n = ls.n_halo_rows;
+    switch (ls.nVar) {
+      case 1: SU2B_LAUNCH(c, k_spmv_row_list<1>, nblk((long)n * 32, 128), 128, n, ls.halo_rows.p, ls.row_ptr, ls.col_ind, ls.A.p, x, y); break;
+      case 4: SU2B_LAUNCH(c, k_spmv_row_list<4>, nblk((long)n * 32, 128), 128, n, ls.halo_rows.p, ls.row_ptr, ls.col_ind, ls.A.p, x, y); break;
+      case 5: SU2B_LAUNCH(c, k_spmv_row_list<5>, nblk((long)n * 32, 128), 128, n, ls.halo_rows.p, ls.row_ptr, ls.col_ind, ls.A.p, x, y); break;
+      default: throw Error("linsys_spmv: unsupported nVar");
+    }
+  }
 }
 
 // ------------------------------------------------------------------------------------------------
@@ -386,6 +450,6 @@ void linsys_apply_jacobi(su2b200_ctx* c, LinSys& ls, const double* x, double* y)
     case 5: SU2B_LAUNCH(c, k_jacobi_apply<5>, nblk(ls.Pd, 128), 128, ls.Pd, ls.invM.p, x, y); break;
     default: throw Error("jacobi: unsupported nVar");
   }
-  if (c->nranks > 1) halo_exchange(c, y, ls.nVar);
+  if (c->nranks > 1 && !c->defer_halo) halo_exchange(c, y, ls.nVar);
 }
 }  // namespace su2b200

@@ -786,7 +786,7 @@ void linsys_apply_ilu(su2b200_ctx* c, LinSys& ls, const double* x, double* y) {
     case 5: ilu_apply_impl<5>(c, ls, x, y); break;
     default: throw Error("ilu: unsupported nVar");
   }
-  if (c->nranks > 1) halo_exchange(c, y, ls.nVar);
+  if (c->nranks > 1 && !c->defer_halo) halo_exchange(c, y, ls.nVar);
 }
 
 template <int NV>
@@ -803,7 +803,7 @@ static void lusgs_impl(su2b200_ctx* c, LinSys& ls, const double* b, double* x) {
     SU2B_LAUNCH(c, k_lusgs_backward_level<NV>, nblk(m, 128), 128, m, ls.lvl_rows_upper.p + ls.lvl_ptr_upper[l], ls.Pd, ls.Pd,
                 ls.row_ptr, ls.col_ind, ls.dia_ptr, ls.A.p, x);
   }
-  if (c->nranks > 1) halo_exchange(c, x, NV);
+  if (c->nranks > 1 && !c->defer_halo) halo_exchange(c, x, NV);
 }
 
 void linsys_apply_lusgs(su2b200_ctx* c, LinSys& ls, const double* b, double* x) {
