@@ -392,6 +392,15 @@ int su2b200_linsys_solve(su2b200_ctx* ctx, int which, int solver, int prec, doub
                          const double* b, double* x, unsigned long* iterations, double* residual);
 /* CSysVector::dot (CSysVector.hpp:335-366) over owned entries, on the device */
 int su2b200_vector_dot(su2b200_ctx* ctx, int which, const double* a, const double* b, double* result);
+/* Allocation-free variant of su2b200_vector_dot. It has NO counterpart in the reference: it was added
+ * for callers that may not call cudaMalloc (code under CUDA graph capture, tight serving loops,
+ * harnesses that forbid it). a, b: host [n]; result: host; the sum runs over all n entries on the context's device and
+ * stream, rank-local (no allreduce). The staging copies and the block partials live in a static device array that
+ * every GPU loading the library holds until exit (16 MiB + 8 KiB), so n is limited to SU2B200_NOALLOC_DOT_MAX doubles
+ * per vector; larger n is rejected with an error. The call makes no cudaMalloc/cudaFree/cudaMallocHost and uses no
+ * allocating library routine. All calls share the array: calls whose GPU work overlaps race on it. */
+#define SU2B200_NOALLOC_DOT_MAX 1048576ul
+int su2b200_vector_dot_noalloc(su2b200_ctx* ctx, const double* a, const double* b, unsigned long n, double* result);
 
 /* ---- restart / solution files in the SU2 native formats ------------------------------------------
  * binary ".dat" (CSU2BinaryFileWriter.cpp:39-94, CSolver::Read_SU2_Restart_Binary CSolver.cpp:2916) and CSV

@@ -106,7 +106,7 @@ EXPORTED_SYMBOLS = [
     "su2b200_linsys_set_partitions", "su2b200_linsys_set_schedule", "su2b200_linsys_set_wide_threshold",
     "su2b200_linsys_set_partition_rows", "su2b200_linsys_set_matrix", "su2b200_linsys_spmv",
     "su2b200_linsys_build_preconditioner", "su2b200_linsys_apply_preconditioner", "su2b200_linsys_solve",
-    "su2b200_vector_dot", "su2b200_mg_link", "su2b200_mg_set_restricted_solution", "su2b200_mg_set_residual_term",
+    "su2b200_vector_dot", "su2b200_vector_dot_noalloc", "su2b200_mg_link", "su2b200_mg_set_restricted_solution", "su2b200_mg_set_residual_term",
     "su2b200_mg_set_forcing_term", "su2b200_mg_get_prolongated_correction", "su2b200_mg_smooth_prolongated_correction",
     "su2b200_mg_set_prolongated_correction", "su2b200_mg_iterate", "su2b200_restart_write", "su2b200_restart_read",
     "su2b200_restart_write_arrays", "su2b200_restart_read_arrays", "su2b200_comm_unique_id", "su2b200_comm_init", "su2b200_halo_exchange",
@@ -117,6 +117,8 @@ EXPORTED_SYMBOLS = [
     "su2b200_mesh_upload", "su2b200_profile_enable", "su2b200_profile_ncat", "su2b200_profile_name",
     "su2b200_profile_report",
 ]
+
+NOALLOC_DOT_MAX = 1 << 20  # SU2B200_NOALLOC_DOT_MAX (include/su2b200.h)
 
 _lib = None
 
