@@ -387,6 +387,12 @@ int su2b200_linsys_spmv(su2b200_ctx* ctx, int which, const double* x, double* y)
 int su2b200_linsys_build_preconditioner(su2b200_ctx* ctx, int which, int prec);
 /* CPreconditioner::operator()(u,v): ComputeJacobi/ILU/LU_SGSPreconditioner (CSysMatrix.cpp:660-888) */
 int su2b200_linsys_apply_preconditioner(su2b200_ctx* ctx, int which, int prec, const double* x, double* y);
+/* The pair every Krylov iteration runs, `precond(V[i], Z[i]); mat_vec(Z[i], V[i+1]);` (CSysSolve.cpp:533-537 FGMRES,
+ * :342-351 / :376 BCGSTAB): z = M^-1 v, w = A z; v, z, w host [nPoint][nVar]. With ILU0 on a pattern whose upper factor is
+ * the Jacobian's own upper triangle (hexahedral / quadrilateral meshes) the backward sweep hands its sum_{j>i} A_ij z_j to
+ * the product, which then reads only the lower triangle, the diagonal and the halo columns; otherwise the two
+ * operators run one after the other. su2b200_linsys_solve uses the same routine. SU2B200_FUSED_UPPER=0 disables it. */
+int su2b200_linsys_precondition_and_multiply(su2b200_ctx* ctx, int which, int prec, const double* v, double* z, double* w);
 /* CSysSolve::Solve (CSysSolve.cpp:1318): b,x host [nPoint][nVar]; x0 = 0 */
 int su2b200_linsys_solve(su2b200_ctx* ctx, int which, int solver, int prec, double tol, int max_iter,
                          const double* b, double* x, unsigned long* iterations, double* residual);

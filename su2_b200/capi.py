@@ -105,7 +105,7 @@ EXPORTED_SYMBOLS = [
     "su2b200_turb_complete_implicit", "su2b200_turb_postprocessing", "su2b200_iterate", "su2b200_linsys_create",
     "su2b200_linsys_set_partitions", "su2b200_linsys_set_schedule", "su2b200_linsys_set_wide_threshold",
     "su2b200_linsys_set_partition_rows", "su2b200_linsys_set_matrix", "su2b200_linsys_spmv",
-    "su2b200_linsys_build_preconditioner", "su2b200_linsys_apply_preconditioner", "su2b200_linsys_solve",
+    "su2b200_linsys_build_preconditioner", "su2b200_linsys_apply_preconditioner", "su2b200_linsys_precondition_and_multiply", "su2b200_linsys_solve",
     "su2b200_vector_dot", "su2b200_vector_dot_noalloc", "su2b200_mg_link", "su2b200_mg_set_restricted_solution", "su2b200_mg_set_residual_term",
     "su2b200_mg_set_forcing_term", "su2b200_mg_get_prolongated_correction", "su2b200_mg_smooth_prolongated_correction",
     "su2b200_mg_set_prolongated_correction", "su2b200_mg_iterate", "su2b200_restart_write", "su2b200_restart_read",

@@ -320,6 +320,8 @@ static void linsys_bind(su2b200_ctx* c, int which, int nVar) {
   ls.h_dia_ptr = g.h_dia_ptr;
   ls.levels_ready = false;
   ls.n_halo_rows = -1;
+  ls.rest_halo_ready = false;
+  ls.upper_prod_of = nullptr;
   ls.h_parts.clear();
   ls.A.alloc((size_t)g.nnz * nVar * nVar);
   ls.A.zero();

@@ -856,6 +856,24 @@ int su2b200_linsys_apply_preconditioner(su2b200_ctx* c, int which, int prec, con
   API_END
 }
 
+int su2b200_linsys_precondition_and_multiply(su2b200_ctx* c, int which, int prec, const double* v, double* z, double* w) {
+  API_BEGIN
+  auto& ls = get_sys(c, which);
+  const size_t n = ls.vecLen();
+  double* dv = ls.vec(0).p;
+  double* dz = ls.vec(1).p;
+  double* dw = ls.vec(2).p;
+  SU2B_CUDA(cudaMemcpyAsync(dv, v, n * sizeof(double), cudaMemcpyHostToDevice, c->stream));
+  SU2B_CUDA(cudaMemsetAsync(dz, 0, n * sizeof(double), c->stream));
+  SU2B_CUDA(cudaMemsetAsync(dw, 0, n * sizeof(double), c->stream));
+  linsys_prec_then_product(c, ls, prec, dv, dz, dw);
+  linsys_check_sweeps(c, ls);
+  SU2B_CUDA(cudaMemcpyAsync(z, dz, n * sizeof(double), cudaMemcpyDeviceToHost, c->stream));
+  SU2B_CUDA(cudaMemcpyAsync(w, dw, n * sizeof(double), cudaMemcpyDeviceToHost, c->stream));
+  SU2B_CUDA(cudaStreamSynchronize(c->stream));
+  API_END
+}
+
 int su2b200_linsys_solve(su2b200_ctx* c, int which, int solver, int prec, double tol, int max_iter, const double* b,
                          double* x, unsigned long* iterations, double* residual) {
   API_BEGIN

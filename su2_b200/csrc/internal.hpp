@@ -174,6 +174,14 @@ struct LinSys {
   dvec<double> scalars;              // device scalars for reductions
   double* h_scalars = nullptr;       // pinned host mirror
   double* h_mgs = nullptr;           // pinned: Hessenberg column of the device Gram-Schmidt
+  // fused upper product: a backward ILU sweep whose upper factor is the Jacobian's upper triangle (upper_stable) computes
+  // sum_{j>i} A_ij z_j on its way; the product A z that follows in a Krylov iteration then only reads the lower triangle,
+  // the diagonal and the halo columns (4 of 7 blocks on a hexahedral mesh) and adds it
+  dvec<double> upper_prod;               // [Pd][nVar]
+  const double* upper_prod_of = nullptr; // the vector z it belongs to (set by the apply, cleared by the next apply)
+  bool want_upper_prod = false;          // set by the Krylov solver around apply + product
+  dvec<int> rest_halo_ptr;               // per owned row: first entry with a halo column (multi-rank only)
+  bool rest_halo_ready = false;
   // owned rows with at least one halo column (multi-rank): redone by the overlapped product once the halos arrived
   dvec<int> halo_rows;
   int n_halo_rows = -1;              // -1: not built yet

@@ -37,6 +37,7 @@ void linsys_apply_ilu(su2b200_ctx* c, LinSys& ls, const double* x, double* y);
 void linsys_apply_lusgs(su2b200_ctx* c, LinSys& ls, const double* x, double* y);
 void linsys_build_prec(su2b200_ctx* c, LinSys& ls, int prec);
 void linsys_apply_prec(su2b200_ctx* c, LinSys& ls, int prec, const double* x, double* y);
+void linsys_prec_then_product(su2b200_ctx* c, LinSys& ls, int prec, const double* v, double* z, double* w);  // z = M^-1 v, w = A z
 void linsys_check_sweeps(su2b200_ctx* c, LinSys& ls);  // throws if the sweep watchdog fired
 void ilu_apply_poll(su2b200_ctx* c, LinSys& ls, const double* x, double* y);  // precond_poll.cu
 bool factor_symbolic(LinSys& ls);                                             // precond_factor.cu

@@ -213,6 +213,23 @@ static void mod_gram_schmidt_device(su2b200_ctx* c, LinSys& ls, int i, VecFn V, 
   for (int k = 0; k <= i + 1; ++k) hcol[k] = ls.h_mgs[8 + k];
 }
 
+// z = M^-1 v, w = A z: the pair every Krylov iteration runs.  The ILU backward sweep is asked for the upper part of the
+// product on its way (LinSys::upper_prod; used when the upper factor is the Jacobian's own upper triangle), the product
+// then reads 4 of the 7 blocks of a hexahedral row.  Summation order of (A z)_i: lower, diagonal, (upper sum), halo
+// columns -- the reference's RowProduct adds the upper products one by one; the difference is one rounding per row.
+void linsys_prec_then_product(su2b200_ctx* c, LinSys& ls, int prec, const double* v, double* z, double* w) {
+  ls.want_upper_prod = (prec == SU2B200_PREC_ILU);
+  try {
+    linsys_apply_prec(c, ls, prec, v, z);
+  } catch (...) {
+    ls.want_upper_prod = false;
+    throw;
+  }
+  ls.want_upper_prod = false;
+  linsys_spmv_exchange_x(c, ls, z, w);
+  ls.upper_prod_of = nullptr;
+}
+
 static unsigned long fgmres(su2b200_ctx* c, LinSys& ls, int prec, double tol, int m, const double* b, double* x,
                             bool xIsZero, double* residual) {
   SU2B_REQUIRE(m >= 1, "Number of linear solver iterations must be greater than 0.");
@@ -243,8 +260,7 @@ static unsigned long fgmres(su2b200_ctx* c, LinSys& ls, int prec, double tol, in
   int i = 0;
   for (i = 0; i < m; i++) {
     if (beta < tol * norm0) break;
-    linsys_apply_prec(c, ls, prec, V(i), Z(i));
-    linsys_spmv_exchange_x(c, ls, Z(i), V(i + 1));
+    linsys_prec_then_product(c, ls, prec, V(i), Z(i), V(i + 1));
     // ModGramSchmidt(i, H, V)
     {
       std::vector<double> hcol(i + 2, 0.0);
@@ -310,14 +326,12 @@ static unsigned long bcgstab(su2b200_ctx* c, LinSys& ls, int prec, double tol, i
     rho = vec_dot(c, ls, r, r_0);
     const double beta = (rho / rho_prime) * (alpha / omega);
     SU2B_LAUNCH(c, k_bcg_p, vgrid(n), 256, n, beta, omega, v, r, p);
-    linsys_apply_prec(c, ls, prec, p, z);
-    linsys_spmv_exchange_x(c, ls, z, v);
+    linsys_prec_then_product(c, ls, prec, p, z, v);
     const double r_0_v = vec_dot(c, ls, r_0, v);
     alpha = rho / r_0_v;
     vec_axpy(c, n, alpha, z, x);
     vec_axpy(c, n, -alpha, v, r);
-    linsys_apply_prec(c, ls, prec, r, z);
-    linsys_spmv_exchange_x(c, ls, z, A_x);
+    linsys_prec_then_product(c, ls, prec, r, z, A_x);
     omega = vec_dot(c, ls, A_x, A_x);
     if (omega == 0.0) break;
     omega = vec_dot(c, ls, A_x, r) / omega;

@@ -254,8 +254,81 @@ __global__ void __launch_bounds__(256) k_spmv_scalar(int Pd, const int* __restri
   if (row < Pd && l == 0) y[row] = acc;
 }
 
+// y = A x for an x that just left the ILU backward sweep together with u_i = sum_{j>i, owned} A_ij x_j (LinSys::upper_prod):
+// only the lower triangle, the diagonal and the halo columns are multiplied here.  Same lane mapping as k_spmv_rows.
+template <int NV>
+__global__ void __launch_bounds__(128, SPMV_ROWS_MIN_BLOCKS) k_spmv_rows_rest(int Pd, const int* __restrict__ row_ptr,
+                                                                              const int* __restrict__ dia_ptr,
+                                                                              const int* __restrict__ halo_ptr,
+                                                                              const int* __restrict__ col_ind,
+                                                                              const double* __restrict__ A,
+                                                                              const double* __restrict__ x,
+                                                                              const double* __restrict__ upper,
+                                                                              double* __restrict__ y) {
+  constexpr int LPB = NV * NV, RPW = 32 / NV;
+  const int lane = threadIdx.x & 31, sub = lane / NV, r = lane % NV;
+  const long wg = ((long)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+  const long row = wg * RPW + sub;
+  const bool on = sub < RPW && row < Pd;
+  const int kb = on ? row_ptr[row] : 0, kd = on ? dia_ptr[row] + 1 : 0;
+  const int ke = on ? row_ptr[row + 1] : 0, kh = (on && halo_ptr) ? halo_ptr[row] : ke;
+  const double up = on ? upper[(size_t)row * NV + r] : 0.0;
+  double acc = 0.0;
+  for (int k = kb; k < kd; ++k) {
+    const int col = col_ind[k];
+    double a[NV], xv[NV];
+#pragma unroll
+    for (int c = 0; c < NV; ++c) a[c] = A[(size_t)k * LPB + r * NV + c];
+#pragma unroll
+    for (int c = 0; c < NV; ++c) xv[c] = x[(size_t)col * NV + c];
+#pragma unroll
+    for (int c = 0; c < NV; ++c) acc += a[c] * xv[c];
+  }
+  acc += up;
+  for (int k = kh; k < ke; ++k) {
+    const int col = col_ind[k];
+#pragma unroll
+    for (int c = 0; c < NV; ++c) acc += A[(size_t)k * LPB + r * NV + c] * x[(size_t)col * NV + c];
+  }
+  if (on) y[(size_t)row * NV + r] = acc;
+}
+
+static bool spmv_fused_upper(su2b200_ctx* c, LinSys& ls, const double* x, double* y) {
+  static const bool enabled = !(getenv("SU2B200_FUSED_UPPER") && atoi(getenv("SU2B200_FUSED_UPPER")) == 0);
+  if (!enabled || ls.nVar == 1 || ls.upper_prod_of != x || x == nullptr) return false;
+  ls.upper_prod_of = nullptr;  // one product per apply: whoever changes x afterwards is not tracked
+  const int* hp = nullptr;
+  if (ls.P > ls.Pd) {
+    if (!ls.rest_halo_ready) {
+      std::vector<int> h(ls.Pd);
+      for (int i = 0; i < ls.Pd; ++i) {
+        int ke = ls.h_row_ptr[i + 1];
+        while (ke > ls.h_dia_ptr[i] + 1 && ls.h_col_ind[ke - 1] >= ls.Pd) --ke;
+        h[i] = ke;
+      }
+      ls.rest_halo_ptr.upload(h);
+      ls.rest_halo_ready = true;
+    }
+    hp = ls.rest_halo_ptr.p;
+  }
+  const long warps = ((long)ls.Pd + 32 / ls.nVar - 1) / (32 / ls.nVar);
+  if (ls.nVar == 4)
+    SU2B_LAUNCH(c, k_spmv_rows_rest<4>, nblk(warps * 32, 128), 128, ls.Pd, ls.row_ptr, ls.dia_ptr, hp, ls.col_ind, ls.A.p, x,
+                (const double*)ls.upper_prod.p, y);
+  else if (ls.nVar == 5)
+    SU2B_LAUNCH(c, k_spmv_rows_rest<5>, nblk(warps * 32, 128), 128, ls.Pd, ls.row_ptr, ls.dia_ptr, hp, ls.col_ind, ls.A.p, x,
+                (const double*)ls.upper_prod.p, y);
+  else
+    return false;
+  return true;
+}
+
 void linsys_spmv(su2b200_ctx* c, LinSys& ls, const double* x, double* y) {
   ProfScope prof_(c, PROF_SPMV);
+  if (spmv_fused_upper(c, ls, x, y)) {
+    if (c->nranks > 1 && !c->defer_halo) halo_exchange(c, y, ls.nVar);
+    return;
+  }
   const long threads = (long)ls.Pd * 32;
   static const int rowsK = getenv("SU2B200_SPMV_ROWS") ? atoi(getenv("SU2B200_SPMV_ROWS")) : 1;
   if (rowsK && ls.nVar > 1) {

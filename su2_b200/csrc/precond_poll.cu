@@ -112,7 +112,9 @@ template <int NV, bool FORWARD>
 __global__ void __launch_bounds__(128) k_poll_sweep(int n, const int4* __restrict__ meta, int* ctrl,
                                                     const int* __restrict__ col_ind, const double* __restrict__ ILU,
                                                     const double* __restrict__ invM, const double* __restrict__ in,
-                                                    double* out) {
+                                                    double* out, double* sout) {
+  // sout (backward sweep only, may be null): receives sum_{j>i} U_ij x_j of every row, the upper part of the product
+  // A x when U_ij == A_ij (linalg.cu: linsys_spmv with the fused upper product)
   constexpr int LPB = NV * NV;
   constexpr int CH = RowData<NV>::CH;
   const int lane = threadIdx.x & 31;
@@ -165,6 +167,7 @@ __global__ void __launch_bounds__(128) k_poll_sweep(int n, const int4* __restric
     if (FORWARD) {
       if (lane < LPB && cc == 0) st_relaxed(out + (size_t)i * NV + r, cur.rhs - s);
     } else {
+      if (sout && lane < LPB && cc == 0) sout[(size_t)i * NV + r] = s;
       const double aux_r = cur.rhs - s;  // valid on lanes r*NV
       const double aux_c = __shfl_sync(FULLM, aux_r, cc * NV);
       const double prod = cur.minv * aux_c;
@@ -324,7 +327,7 @@ template <int NV, bool FORWARD>
 __global__ void __launch_bounds__(128, ROWS_MIN_BLOCKS) k_poll_sweep_rows(int nGroups, const int4* __restrict__ meta, int* ctrl,
                                                          const int* __restrict__ col_ind, const double* __restrict__ ILU,
                                                          const double* __restrict__ invM, const double* __restrict__ in,
-                                                         double* out) {
+                                                         double* out, double* sout) {
   constexpr int LPB = NV * NV;
   constexpr int RPW = 32 / NV;  // rows per warp
   constexpr int CH = ROWS_CH;   // entries held in registers (a hex row has 3 on each side); longer rows: tail loop
@@ -378,6 +381,7 @@ __global__ void __launch_bounds__(128, ROWS_MIN_BLOCKS) k_poll_sweep_rows(int nG
     for (int k = 0; k < CH; ++k)
 #pragma unroll
       for (int c = 0; c < NV; ++c) y[k][c] = __shfl_sync(FULLM, mine[k], sub * NV + c);
+    double su = 0.0;
 #pragma unroll
     for (int k = 0; k < CH; ++k) {
       if (on && ok && kb + k < ke) {
@@ -385,6 +389,7 @@ __global__ void __launch_bounds__(128, ROWS_MIN_BLOCKS) k_poll_sweep_rows(int nG
 #pragma unroll
         for (int c = 0; c < NV; ++c) p += a[k][c] * y[k][c];
         v -= p;
+        if (!FORWARD) su += p;
       }
     }
     if (on) {
@@ -397,11 +402,13 @@ __global__ void __launch_bounds__(128, ROWS_MIN_BLOCKS) k_poll_sweep_rows(int nG
           p += ILU[(size_t)idx * LPB + r * NV + c] * yj;
         }
         v -= p;
+        if (!FORWARD) su += p;
       }
     }
     if (FORWARD) {
       if (on && ok) st_relaxed(out + (size_t)i * NV + r, v);
     } else {
+      if (sout && on && ok) sout[(size_t)i * NV + r] = su;
       // x_i = invM_i * aux (MatrixVectorProduct): lane r needs the whole aux vector of its row
       double x = 0.0;
 #pragma unroll
@@ -432,7 +439,7 @@ template <int NV, bool FORWARD, int U>
 __global__ void __launch_bounds__(128, ROWSU_MIN_BLOCKS) k_poll_sweep_rowsU(int nIters, const int4* __restrict__ meta, int* ctrl,
                                                           const int* __restrict__ col_ind, const double* __restrict__ ILU,
                                                           const double* __restrict__ invM, const double* __restrict__ in,
-                                                          double* out) {
+                                                          double* out, double* sout) {
   constexpr int LPB = NV * NV, RPW = 32 / NV, CH = ROWS_CH;
   const int lane = threadIdx.x & 31;
   const int sub = lane / NV, r = lane % NV;
@@ -467,7 +474,7 @@ __global__ void __launch_bounds__(128, ROWSU_MIN_BLOCKS) k_poll_sweep_rowsU(int 
     }
     // everything that does not depend on the sweep: block rows, rhs (and the inverse diagonal), for all U groups
     bool on[U];
-    double a[U][CH][NV], v[U], dinv[U][NV], mine[U][CH];
+    double a[U][CH][NV], v[U], dinv[U][NV], mine[U][CH], su[U];
 #pragma unroll
     for (int u = 0; u < U; ++u) {
       on[u] = ok && m0[u].x >= 0;
@@ -479,6 +486,7 @@ __global__ void __launch_bounds__(128, ROWSU_MIN_BLOCKS) k_poll_sweep_rowsU(int 
         for (int c = 0; c < NV; ++c) a[u][k][c] = has ? ILU[(size_t)(m0[u].y + k) * LPB + r * NV + c] : 0.0;
       }
       v[u] = on[u] ? in[(size_t)m0[u].x * NV + r] : 0.0;
+      su[u] = 0.0;
       if (!FORWARD) {
 #pragma unroll
         for (int c = 0; c < NV; ++c) dinv[u][c] = on[u] ? invM[(size_t)m0[u].x * LPB + r * NV + c] : 0.0;
@@ -514,6 +522,7 @@ __global__ void __launch_bounds__(128, ROWSU_MIN_BLOCKS) k_poll_sweep_rowsU(int 
 #pragma unroll
           for (int c = 0; c < NV; ++c) p += a[u][k][c] * y[c];
           v[u] -= p;
+          if (!FORWARD) su[u] += p;
         }
       }
     }
@@ -530,11 +539,13 @@ __global__ void __launch_bounds__(128, ROWSU_MIN_BLOCKS) k_poll_sweep_rowsU(int 
             p += ILU[(size_t)idx * LPB + r * NV + c] * yj;
           }
           v[u] -= p;
+          if (!FORWARD) su[u] += p;
         }
       }
       if (FORWARD) {
         if (on[u] && ok) st_relaxed(out + (size_t)i * NV + r, v[u]);
       } else {
+        if (sout && on[u] && ok) sout[(size_t)i * NV + r] = su[u];
         double x = 0.0;
 #pragma unroll
         for (int c = 0; c < NV; ++c) x += dinv[u][c] * __shfl_sync(FULLM, v[u], sub * NV + c);
@@ -765,33 +776,44 @@ static void ilu_apply_poll_impl(su2b200_ctx* c, LinSys& ls, const double* x, dou
       constexpr int UNIT = ROWS_U * (32 / NV);
       static const int capU = getenv("SU2B200_SWEEP_BLOCKS_U") ? atoi(getenv("SU2B200_SWEEP_BLOCKS_U")) : 0;
       static const int useU = getenv("SU2B200_SWEEP_U") ? atoi(getenv("SU2B200_SWEEP_U")) : ROWS_U;
+      // fused upper product (linalg.cu): the backward sweep leaves sum_{j>i} U_ij y_j per row when the caller asked for it
+      // and the upper factor is the Jacobian's own upper triangle
+      double* sout = nullptr;
+      ls.upper_prod_of = nullptr;
+      if (ls.want_upper_prod && ls.upper_stable && ls.nparts <= 1 && ls.ilu_gen == ls.A_gen) {
+        if (ls.upper_prod.n != (size_t)ls.Pd * NV) ls.upper_prod.alloc((size_t)ls.Pd * NV);
+        sout = ls.upper_prod.p;
+      }
       auto sweep = [&](auto narrowK, auto wideK, auto wideK1, const int4* mnar, const int4* mwid, const int (&sp)[4],
-                       const double* ilu, const double* src, double* dst) {
+                       const double* ilu, const double* src, double* dst, double* sout) {
         const int nRows = ls.Pd;
-        if (sp[0] > 0) launch_resident(c, narrowK, (sp[0] + 3) / 4, capB, sp[0], mnar, ctrl, ci, ilu, invM, src, dst);
+        if (sp[0] > 0) launch_resident(c, narrowK, (sp[0] + 3) / 4, capB, sp[0], mnar, ctrl, ci, ilu, invM, src, dst, sout);
         if (sp[3] > sp[1]) {
           if (useU == 1)  // A/B: one group per iteration over the same padded list (every unit is ROWS_U groups)
             launch_resident(c, wideK1, ((sp[3] - sp[1]) * ROWS_U + 3) / 4, capU, (sp[3] - sp[1]) * ROWS_U,
-                            mwid + (size_t)sp[1] * UNIT, ctrl, ci, ilu, invM, src, dst);
+                            mwid + (size_t)sp[1] * UNIT, ctrl, ci, ilu, invM, src, dst, sout);
           else
             launch_resident(c, wideK, (sp[3] - sp[1] + 3) / 4, capU, sp[3] - sp[1], mwid + (size_t)sp[1] * UNIT, ctrl, ci,
-                            ilu, invM, src, dst);
+                            ilu, invM, src, dst, sout);
         }
         if (nRows > sp[2])
-          launch_resident(c, narrowK, (nRows - sp[2] + 3) / 4, capB, nRows - sp[2], mnar + sp[2], ctrl, ci, ilu, invM, src, dst);
+          launch_resident(c, narrowK, (nRows - sp[2] + 3) / 4, capB, nRows - sp[2], mnar + sp[2], ctrl, ci, ilu, invM, src, dst,
+                          sout);
       };
       sweep(k_poll_sweep<NV, true>, k_poll_sweep_rowsU<NV, true, ROWS_U>, k_poll_sweep_rowsU<NV, true, 1>, ml, mrl,
-            ls.poll_split_lower, ilu, x, w);
+            ls.poll_split_lower, ilu, x, w, (double*)nullptr);
       sweep(k_poll_sweep<NV, false>, k_poll_sweep_rowsU<NV, false, ROWS_U>, k_poll_sweep_rowsU<NV, false, 1>, mu, mru,
-            ls.poll_split_upper, iluU, (const double*)w, y);
+            ls.poll_split_upper, iluU, (const double*)w, y, sout);
+      if (sout) ls.upper_prod_of = y;
     } else if (pipe) {
       const size_t smem = (size_t)4 * PIPE * sizeof(SweepStage<NV>);
       launch_resident_smem(c, k_poll_sweep_pipe<NV, true>, smem, (ls.Pd + 3) / 4, capB, ls.Pd, ml, ctrl, ci, ilu, invM, x, w);
       launch_resident_smem(c, k_poll_sweep_pipe<NV, false>, smem, (ls.Pd + 3) / 4, capB, ls.Pd, mu, ctrl, ci, iluU, invM,
                            (const double*)w, y);
     } else {
-      launch_resident(c, k_poll_sweep<NV, true>, (ls.Pd + 3) / 4, capB, ls.Pd, ml, ctrl, ci, ilu, invM, x, w);
-      launch_resident(c, k_poll_sweep<NV, false>, (ls.Pd + 3) / 4, capB, ls.Pd, mu, ctrl, ci, iluU, invM, (const double*)w, y);
+      launch_resident(c, k_poll_sweep<NV, true>, (ls.Pd + 3) / 4, capB, ls.Pd, ml, ctrl, ci, ilu, invM, x, w, (double*)nullptr);
+      launch_resident(c, k_poll_sweep<NV, false>, (ls.Pd + 3) / 4, capB, ls.Pd, mu, ctrl, ci, iluU, invM, (const double*)w, y,
+                      (double*)nullptr);
     }
   }
 }

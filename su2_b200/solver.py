@@ -456,6 +456,13 @@ class LinearSystem:
                                             int(max_iter), ptr_d(b), ptr_d(x), C.byref(it), C.byref(res)))
         return x, it.value, res.value
 
+    def PreconditionAndMultiply(self, prec, v):
+        """z = M^-1 v, w = A z (one Krylov iteration's operator pair; fused upper product where the pattern allows)."""
+        v = as_f64(v).ravel()
+        z, w = np.empty_like(v), np.empty_like(v)
+        check(self.lib.su2b200_linsys_precondition_and_multiply(self.ctx, self.which, int(prec), ptr_d(v), ptr_d(z), ptr_d(w)))
+        return z, w
+
     def dot(self, a, b):
         a, b = as_f64(a).ravel(), as_f64(b).ravel()
         r = C.c_double()

@@ -171,3 +171,34 @@ def test_jacobi_and_lusgs_against_the_oracle():
             assert np.max(np.abs(z - zr)) <= 1e-12 * np.max(np.abs(zr))
         finally:
             ls.close()
+
+
+@pytest.mark.parametrize("n,tets", CASES)
+@pytest.mark.parametrize("nv", [4, 5])
+def test_precondition_and_multiply_equals_the_two_operators(n, tets, nv):
+    """z = M^-1 v, w = A z in one call (the fused upper product on the hexahedral pattern, the plain sequence on the
+    tetrahedral one, where fill-in modifies upper blocks) against ApplyPreconditioner + MatrixVectorProduct and the
+    oracle. The fused product adds the upper part of a row as one pre-summed term: one rounding per row apart."""
+    rng = np.random.default_rng(300 + nv + (7 if tets else 0))
+    P, rp, ci, dp = _pattern(n, tets)
+    A = _matrix(rng, rp, ci, dp, nv)
+    ls = LinearSystem(nv, P, P, rp, ci)
+    try:
+        ls.set_matrix(A)
+        ilu, invM = lo.ilu0_build(rp, ci, dp, A)
+        for prec in (capi.PREC_ILU, capi.PREC_JACOBI):
+            ls.BuildPreconditioner(prec)
+            for rep in range(2):  # twice: the second call finds the buffers of the first
+                v = rng.standard_normal(P * nv)
+                z, w = ls.PreconditionAndMultiply(prec, v)
+                z2 = ls.ApplyPreconditioner(prec, v)
+                w2 = ls.MatrixVectorProduct(z2)
+                assert np.array_equal(z, z2)
+                assert np.max(np.abs(w - w2)) <= 1e-14 * np.max(np.abs(w2))
+                if prec == capi.PREC_ILU:
+                    zr = lo.ilu0_apply(rp, ci, dp, ilu, invM, v).ravel()
+                    wr = lo.block_spmv(rp, ci, A, zr).ravel()
+                    assert np.max(np.abs(z - zr)) <= 1e-13 * np.max(np.abs(zr))
+                    assert np.max(np.abs(w - wr)) <= 1e-13 * np.max(np.abs(wr))
+    finally:
+        ls.close()
