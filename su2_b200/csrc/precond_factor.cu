@@ -392,6 +392,47 @@ __device__ __forceinline__ bool is_sentinel(double v) {
   return (unsigned)__double2hiint(v) == (unsigned)(SENTINEL >> 32);
 }
 
+// Inverse of a block by Gauss elimination (CSysMatrix::MatrixInverse), nVar lanes per block: lane r holds ROW r of the block
+// being eliminated (ar) and builds COLUMN r of the inverse (mc): the elimination weights (one division per lane and
+// pivot) and the pivot rows travel by shuffle, every update of the inverse is then local to the lane that owns the
+// column, and the closing divisions run on all columns at once.  All 32 lanes call it (gbase = first lane of the group).
+template <int NV>
+__device__ __forceinline__ void invert_block_rows(double (&ar)[NV], double (&mc)[NV], int gbase, int r) {
+#pragma unroll
+  for (int c = 0; c < NV; ++c) mc[c] = (r == c) ? 1.0 : 0.0;
+#pragma unroll
+  for (int jp = 0; jp < NV - 1; ++jp) {
+    double prow[NV];
+#pragma unroll
+    for (int c = jp; c < NV; ++c) prow[c] = __shfl_sync(FULLM, ar[c], gbase + jp);
+    double pj = prow[jp];
+    fix_pivot(pj);
+    if (r == jp) ar[jp] = pj;
+    double wgt = 0.0;
+    if (r > jp) {
+      wgt = ar[jp] / pj;
+#pragma unroll
+      for (int c = jp; c < NV; ++c) ar[c] -= wgt * (c == jp ? pj : prow[c]);
+    }
+#pragma unroll
+    for (int m = jp + 1; m < NV; ++m) {
+      const double wm = __shfl_sync(FULLM, wgt, gbase + m);
+      if (r <= jp) mc[m] -= wm * mc[jp];
+    }
+  }
+#pragma unroll
+  for (int ip = NV - 1; ip >= 0; --ip) {
+#pragma unroll
+    for (int jp = ip + 1; jp < NV; ++jp) {
+      const double a = __shfl_sync(FULLM, ar[jp], gbase + ip);
+      mc[ip] -= a * mc[jp];
+    }
+    double pii = __shfl_sync(FULLM, ar[ip], gbase + ip);
+    fix_pivot(pii);
+    mc[ip] /= pii;
+  }
+}
+
 #ifndef FACTOR_ROWS_MIN_BLOCKS
 #define FACTOR_ROWS_MIN_BLOCKS 3  // resident blocks per SM the register allocation aims at
 #endif
@@ -436,6 +477,115 @@ __global__ void __launch_bounds__(128, FACTOR_ROWS_MIN_BLOCKS) k_factor_rows(int
     const int i = d.a.x, rb = d.a.y, di = d.a.z, re = d.a.w;
     const bool on = ok && i >= 0;
     const int nOwn = on ? re - rb : 0, nl = on ? di - rb : 0, nOps = on ? d.b.y : 0;
+    // ---- regular groups: straight-line code ------------------------------------------------------------------------
+    // Every row of the warp has at most RG lower neighbours, exactly one update per lower neighbour, landing on the
+    // diagonal block, from a stable staged source (any mesh without triangles in its graph: hexahedra, quadrilaterals;
+    // flagged per row by factor_symbolic).  D_i = A_ii - sum_k (A_ik invD_k) A_ki then needs no update lists, no slot
+    // searches and no loops of data-dependent length: ~2800 warp instructions per group in the general code below, of
+    // which 260 are DFMA (ncu, profiles/r02_ncu_factor_rows.txt).  Same operations in the same order.
+    if (slim && __all_sync(FULLM, !live || (d.b.w & 2))) {
+      constexpr int RG = 3;
+#pragma unroll
+      for (int s = 0; s <= RG; ++s)
+        if (on && s <= nl) {
+#pragma unroll
+          for (int c = 0; c < NV; ++c) cp_async8(T + s * LPB + r * NV + c, A + (size_t)(rb + s) * LPB + r * NV + c);
+        }
+      int jc[RG];
+      unsigned src[RG];
+#pragma unroll
+      for (int k = 0; k < RG; ++k) {
+        jc[k] = k < nl ? col_ind[rb + k] : 0;
+        src[k] = k < nl ? ((unsigned)ops[d.b.x + k].x & ~STABLE) : 0u;
+      }
+      double inv[RG][NV];
+#pragma unroll
+      for (int k = 0; k < RG; ++k)
+#pragma unroll
+        for (int c = 0; c < NV; ++c) inv[k][c] = k < nl ? ldr(invM + (size_t)jc[k] * LPB + r * NV + c) : 0.0;
+#pragma unroll
+      for (int k = 0; k < RG; ++k)
+        if (k < nl) {
+#pragma unroll
+          for (int c = 0; c < NV; ++c)
+            cp_async8(T + (ownCap + k) * LPB + r * NV + c, A + (size_t)src[k] * LPB + r * NV + c);
+        }
+      cp_async_commit();
+      // all awaited inverse diagonals at once: one element per row and neighbour is watched, the rest fetched on arrival
+      for (unsigned spins = 0;; ++spins) {
+        bool miss = false;
+#pragma unroll
+        for (int k = 0; k < RG; ++k)
+#pragma unroll
+          for (int c = 0; c < NV; ++c) miss = miss || is_sentinel(inv[k][c]);
+        if (!__any_sync(FULLM, miss)) break;
+#pragma unroll
+        for (int k = 0; k < RG; ++k) {
+          bool mk = false;
+#pragma unroll
+          for (int c = 0; c < NV; ++c) mk = mk || is_sentinel(inv[k][c]);
+          if (mk && !is_sentinel(ldr(invM + (size_t)jc[k] * LPB + (LPB - 1)))) {
+#pragma unroll
+            for (int c = 0; c < NV; ++c)
+              if (is_sentinel(inv[k][c])) inv[k][c] = ldr(invM + (size_t)jc[k] * LPB + r * NV + c);
+          }
+        }
+        if ((spins & 1023u) == 1023u) {
+          if (spins > (1u << 22)) atomicExch(ctrl + 1, 1);
+          if (__any_sync(FULLM, ldr_i(ctrl + 1) != 0)) { ok = false; break; }
+        }
+      }
+      // the inverses go to the tiles behind the diagonal (free in the slim form: the upper blocks are not staged)
+#pragma unroll
+      for (int k = 0; k < RG; ++k)
+        if (k < nl) {
+#pragma unroll
+          for (int c = 0; c < NV; ++c) T[(nl + 1 + k) * LPB + r * NV + c] = inv[k][c];
+        }
+      cp_async_wait<0>();
+      __syncwarp();
+      const bool go = on && ok;
+      double dg[NV], mc[NV];
+#pragma unroll
+      for (int c = 0; c < NV; ++c) dg[c] = go ? T[nl * LPB + r * NV + c] : (r == c ? 1.0 : 0.0);
+#pragma unroll
+      for (int k = 0; k < RG; ++k)
+        if (go && k < nl) {
+          double a[NV], w[NV];
+#pragma unroll
+          for (int m = 0; m < NV; ++m) a[m] = T[k * LPB + r * NV + m];
+          const double* iv = T + (nl + 1 + k) * LPB;
+#pragma unroll
+          for (int c = 0; c < NV; ++c) {
+            double acc = 0.0;
+#pragma unroll
+            for (int m = 0; m < NV; ++m) acc += a[m] * iv[m * NV + c];
+            w[c] = acc;
+          }
+#pragma unroll
+          for (int c = 0; c < NV; ++c) ILU[(size_t)(rb + k) * LPB + r * NV + c] = w[c];
+          const double* sp = T + (ownCap + k) * LPB;
+#pragma unroll
+          for (int c = 0; c < NV; ++c) {
+            double acc = 0.0;
+#pragma unroll
+            for (int m = 0; m < NV; ++m) acc += w[m] * sp[m * NV + c];
+            dg[c] -= acc;
+          }
+        }
+      if (go) {
+#pragma unroll
+        for (int c = 0; c < NV; ++c) ILU[(size_t)(rb + nl) * LPB + r * NV + c] = dg[c];
+      }
+      invert_block_rows<NV>(dg, mc, sub * NV, r);
+      if (go) {
+#pragma unroll
+        for (int m = 0; m < NV; ++m) str(invM + (size_t)i * LPB + m * NV + r, mc[m]);
+      }
+      __syncwarp();
+      ok = __all_sync(FULLM, ok);
+      continue;
+    }
     // the row itself (asynchronous copies into its tiles), the first update ops and the columns of the lower entries
     // in one round of loads, then the first look at the awaited inverse diagonals (row r of each) and the staged
     // sources: three dependent rounds of memory latency per group instead of one per array
@@ -567,51 +717,16 @@ __global__ void __launch_bounds__(128, FACTOR_ROWS_MIN_BLOCKS) k_factor_rows(int
       __syncwarp();  // invT is rewritten by the next lower entry
     }
     __syncwarp();
-    // inverse of the factored diagonal block: lane r holds row r of A and of the inverse, pivot rows come by shuffle
-    // lane r holds ROW r of the block being eliminated and COLUMN r of the inverse being built: the elimination
-    // weights (one division per lane and pivot) and the pivot rows travel by shuffle, every update of the inverse is
-    // then local to the lane that owns the column, and the closing divisions run on all columns at once
     double ar[NV], mc[NV];
 #pragma unroll
-    for (int c = 0; c < NV; ++c) { ar[c] = (on && ok) ? T[nl * LPB + r * NV + c] : (r == c ? 1.0 : 0.0); mc[c] = (r == c) ? 1.0 : 0.0; }
-    const int gbase = sub * NV;
-#pragma unroll
-    for (int jp = 0; jp < NV - 1; ++jp) {
-      double prow[NV];
-#pragma unroll
-      for (int c = jp; c < NV; ++c) prow[c] = __shfl_sync(FULLM, ar[c], gbase + jp);
-      double pj = prow[jp];
-      fix_pivot(pj);
-      if (r == jp) ar[jp] = pj;
-      double wgt = 0.0;
-      if (r > jp) {
-        wgt = ar[jp] / pj;
-#pragma unroll
-        for (int c = jp; c < NV; ++c) ar[c] -= wgt * (c == jp ? pj : prow[c]);
-      }
-#pragma unroll
-      for (int m = jp + 1; m < NV; ++m) {
-        const double wm = __shfl_sync(FULLM, wgt, gbase + m);
-        if (r <= jp) mc[m] -= wm * mc[jp];
-      }
-    }
-#pragma unroll
-    for (int ip = NV - 1; ip >= 0; --ip) {
-#pragma unroll
-      for (int jp = ip + 1; jp < NV; ++jp) {
-        const double a = __shfl_sync(FULLM, ar[jp], gbase + ip);
-        mc[ip] -= a * mc[jp];
-      }
-      double pii = __shfl_sync(FULLM, ar[ip], gbase + ip);
-      fix_pivot(pii);
-      mc[ip] /= pii;
-    }
+    for (int c = 0; c < NV; ++c) ar[c] = (on && ok) ? T[nl * LPB + r * NV + c] : (r == c ? 1.0 : 0.0);
+    invert_block_rows<NV>(ar, mc, sub * NV, r);
     if (on && ok) {
       const int nw = slim ? nLoad : nOwn;
       for (int s = 0; s < nw; ++s)
 #pragma unroll
         for (int c = 0; c < NV; ++c) ILU[(size_t)(rb + s) * LPB + r * NV + c] = T[s * LPB + r * NV + c];
-      if (d.b.w) __threadfence();
+      if (d.b.w & 1) __threadfence();
 #pragma unroll
       for (int m = 0; m < NV; ++m) str(invM + (size_t)i * LPB + m * NV + r, mc[m]);
     }
@@ -739,8 +854,20 @@ bool factor_symbolic(LinSys& ls) {
           ls.factor_split[0] = ls.lvl_ptr_lower[l];
           ls.factor_split[2] = (int)(padded.size() / rpw);
         }
-        for (int t = ls.lvl_ptr_lower[l]; t < ls.lvl_ptr_lower[l + 1]; ++t) padded.push_back(desc[t]);
-        while (padded.size() % rpw) padded.push_back(empty);
+        for (int t = ls.lvl_ptr_lower[l]; t < ls.lvl_ptr_lower[l + 1]; ++t) {
+          // b.w bit 1: the row qualifies for the straight-line path of k_factor_rows (see there)
+          RowDesc d = desc[t];
+          const int nl = d.a.z - d.a.y;
+          bool reg = nl <= 3 && d.b.y == nl && d.b.w == 0 && 2 * nl + 1 <= maxOwn;
+          for (int u = 0; u < d.b.y && reg; ++u) {
+            const int2 op = opsLevel[d.b.x + u];
+            reg = ((unsigned)op.x & STABLE) && (op.y >> 16) == u && (op.y & 0xffff) == nl;
+          }
+          if (reg && getenv("SU2B200_FACTOR_REGULAR") == nullptr) d.b.w |= 2;
+          else if (reg && atoi(getenv("SU2B200_FACTOR_REGULAR")) != 0) d.b.w |= 2;
+          padded.push_back(d);
+        }
+        { RowDesc e = empty; e.b.w = 2; while (padded.size() % rpw) padded.push_back(e); }
         if (l == last) {
           ls.factor_split[1] = ls.lvl_ptr_lower[l + 1];
           ls.factor_split[3] = (int)(padded.size() / rpw);
