@@ -437,7 +437,7 @@ __device__ __forceinline__ void invert_block_rows(double (&ar)[NV], double (&mc)
 #define FACTOR_ROWS_MIN_BLOCKS 3  // resident blocks per SM the register allocation aims at
 #endif
 template <int NV>
-__global__ void __launch_bounds__(128, FACTOR_ROWS_MIN_BLOCKS) k_factor_rows(int nGroups, int slim, int ownCap, int srcCap, const RowDesc* __restrict__ desc,
+__global__ void __launch_bounds__(128, FACTOR_ROWS_MIN_BLOCKS) k_factor_rows(int nGroups, int slim, int dyn, int ownCap, int srcCap, const RowDesc* __restrict__ desc,
                                                      const int2* __restrict__ ops, int* ctrl,
                                                      const int* __restrict__ col_ind, const double* __restrict__ A,
                                                      double* ILU, double* invM) {
@@ -458,15 +458,29 @@ __global__ void __launch_bounds__(128, FACTOR_ROWS_MIN_BLOCKS) k_factor_rows(int
   RowDesc d1, d2;
   d1.a = d2.a = make_int4(-1, 0, 0, 0);
   d1.b = d2.b = make_int4(0, 0, 0, 0);
+  // Group order: static (warp w takes w, w + W, ...) or, dyn != 0, by ticket (ctrl[0], zeroed by the host): warps differ in
+  // pace (position of their SM relative to the L2 slices and the second die), and with the static order the others end
+  // up polling for the rows of the slowest (6.59 -> 6.39 ms on 185^3).  Tickets are drawn three groups ahead
+  // (descriptors two ahead); a warp works through its tickets in increasing order, so the lowest unfinished group is
+  // always being worked on: no deadlock.
+  auto draw = [&]() {
+    int t = 0;
+    if (lane == 0) t = atomicAdd(ctrl, 1);
+    return __shfl_sync(FULLM, t, 0);
+  };
   const int g0 = blockIdx.x * (blockDim.x >> 5) + wib;
-  if (live && g0 < nGroups) d1 = desc[(size_t)g0 * RPW + sub];
-  if (live && g0 + W < nGroups) d2 = desc[(size_t)(g0 + W) * RPW + sub];
-  for (int g = g0; g < nGroups; g += W) {
+  int t0 = g0, t1 = g0 + W, t2 = g0 + 2 * W, t3 = g0 + 3 * W;
+  if (dyn) { t0 = draw(); t1 = draw(); t2 = draw(); t3 = draw(); }
+  if (live && t0 < nGroups) d1 = desc[(size_t)t0 * RPW + sub];
+  if (live && t1 < nGroups) d2 = desc[(size_t)t1 * RPW + sub];
+  for (int g = t0; g < nGroups; g = t0) {
     const RowDesc d = d1;
     d1 = d2;
     d2.a = make_int4(-1, 0, 0, 0);
     d2.b = make_int4(0, 0, 0, 0);
-    if (live && g + 2 * W < nGroups) d2 = desc[(size_t)(g + 2 * W) * RPW + sub];
+    if (live && t2 < nGroups) d2 = desc[(size_t)t2 * RPW + sub];
+    t0 = t1; t1 = t2; t2 = t3;
+    t3 = dyn ? draw() : t3 + W;
     if (d1.a.x >= 0) {
       const char* nb = reinterpret_cast<const char*>(A + (size_t)d1.a.y * LPB);
       const int bytes = (slim ? d1.a.z - d1.a.y + 1 : d1.a.w - d1.a.y) * LPB * (int)sizeof(double);
@@ -971,7 +985,10 @@ static void factor_launch_rows(su2b200_ctx* c, LinSys& ls, int gbeg, int gend) {
   double* ilu = ls.ilu.p;
   double* invM = ls.invM.p;
   int slim = ls.ilu_slim ? 1 : 0;
-  void* argv[] = {&nGroups, &slim, &ownCap, &srcCap, &desc, &ops, &ctrl, &ci, &A, &ilu, &invM};
+  static const int dynEnv = getenv("SU2B200_FACTOR_DYN") ? atoi(getenv("SU2B200_FACTOR_DYN")) : 1;
+  int dyn = dynEnv;
+  if (dyn) SU2B_CUDA(cudaMemsetAsync(ctrl, 0, sizeof(int), c->stream));
+  void* argv[] = {&nGroups, &slim, &dyn, &ownCap, &srcCap, &desc, &ops, &ctrl, &ci, &A, &ilu, &invM};
   SU2B_CUDA(cudaLaunchCooperativeKernel((const void*)k_factor_rows<NV>, dim3(grid), dim3(128), argv, smem, c->stream));
   c->launches++;
 }
