@@ -431,6 +431,14 @@ int su2b200_restart_read_arrays(const char* path, int nDim, int nTurb, unsigned 
 /* 128-byte ncclUniqueId: rank 0 creates it, the host side broadcasts it (MPI_Bcast / torch.distributed) */
 int su2b200_comm_unique_id(unsigned char id[128]);
 int su2b200_comm_init(su2b200_ctx* ctx, int rank, int size, const unsigned char id[128]);
+/* Optional, after su2b200_comm_init, ranks = processes on one node: allreduces of single doubles inside the Krylov
+ * reduction kernels over peer memory (NVLink/NVSwitch) instead of ncclAllReduce (the role of SU2_MPI::Allreduce in
+ * CSysVector::dot, CSysVector.hpp:335-366, called ~100 times per nonlinear iteration by ModGramSchmidt,
+ * CSysSolve.cpp:179-240). _create returns this rank's 64-byte cudaIpc handle; the caller allgathers the handles
+ * (MPI_Allgather in the reference, torch.distributed here) and passes all of them, in rank order, to _connect.
+ * Without it, or if _connect fails, the NCCL path stays in use. SU2B200_MAILBOX=0 disables it. */
+int su2b200_comm_mailbox_create(su2b200_ctx* ctx, unsigned char handle[64]);
+int su2b200_comm_mailbox_connect(su2b200_ctx* ctx, const unsigned char* handles /*[size][64]*/);
 /* halo exchange of a named per-point array (MPI_QUANTITIES: SOLUTION, PRIMITIVE_GRADIENT, PRIMITIVE_LIMITER, ...):
  * InitiateComms + CompleteComms in one call; count per point = su2b200_array_size / nPoint; no-op on a single rank */
 int su2b200_halo_exchange(su2b200_ctx* ctx, int which_array);

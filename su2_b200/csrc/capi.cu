@@ -71,6 +71,7 @@ int su2b200_destroy(su2b200_ctx* c) {
   if (c->fs.h_counters) cudaFreeHost(c->fs.h_counters);
   cudaEventDestroy(c->ev0);
   cudaEventDestroy(c->ev1);
+  mailbox_release(c);
   if (c->ev_packed) cudaEventDestroy(c->ev_packed);
   if (c->ev_unpacked) cudaEventDestroy(c->ev_unpacked);
   if (c->comm_stream) cudaStreamSynchronize(c->comm_stream);

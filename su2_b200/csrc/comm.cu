@@ -131,6 +131,33 @@ void halo_exchange_finish(su2b200_ctx* c) {
   c->exchange_in_flight = false;
 }
 
+// ---- mailbox allreduce over peer memory ----------------------------------------------------------------------------------
+// The Gram-Schmidt of FGMRES needs ~100 single-double allreduces per nonlinear iteration, each on the critical path
+// (ncclAllReduce in-stream: ~26 us each on 2 GPUs, 2.6 ms of a 70 ms step).  Instead the reduction kernel itself writes
+// its partial sum into every peer's mailbox over NVLink/NVSwitch and reads the peers' sums from its own (kernels.hpp:
+// mailbox_allreduce_block).  The mailboxes are plain cudaMalloc memory shared with cudaIpc handles, which the host side
+// allgathers with whatever it has (torch.distributed in bench.py, MPI in the reference-side shim).
+static constexpr size_t MBOX_WORDS = 16 + (size_t)su2b200_ctx::MBOX_SLOTS * su2b200_ctx::MBOX_MAX_RANKS * 2;
+
+bool mailbox_view(su2b200_ctx* c, MailboxView* v) {
+  if (!c->mbox_ready) return false;
+  v->local = c->mbox_local;
+  v->peers = reinterpret_cast<unsigned long long* const*>(c->mbox_peers.p);
+  v->rank = c->rank;
+  v->nranks = c->nranks;
+  return true;
+}
+
+void mailbox_release(su2b200_ctx* c) {
+  c->mbox_ready = false;
+  for (int r = 0; r < su2b200_ctx::MBOX_MAX_RANKS; ++r) {
+    if (c->mbox_peer_host[r] && r != c->rank) cudaIpcCloseMemHandle(c->mbox_peer_host[r]);
+    c->mbox_peer_host[r] = nullptr;
+  }
+  if (c->mbox_local) cudaFree(c->mbox_local);
+  c->mbox_local = nullptr;
+}
+
 // in-stream, in-place sum of n device doubles over the ranks (no host synchronisation)
 void allreduce_dev_sum(su2b200_ctx* c, double* d, int n) {
   if (c->nranks <= 1) return;
@@ -171,6 +198,52 @@ extern "C" {
 int su2b200_comm_unique_id(unsigned char id[128]) {
   try {
     SU2B_NCCL(nccl().GetUniqueId(id));
+    return 0;
+  } catch (const std::exception& e) { set_error(e.what()); return 1; }
+}
+int su2b200_comm_mailbox_create(su2b200_ctx* c, unsigned char handle[64]) {
+  try {
+    if (!c) throw Error("null context");
+    static_assert(sizeof(cudaIpcMemHandle_t) == 64, "cudaIpcMemHandle_t is 64 bytes");
+    SU2B_CUDA(cudaSetDevice(c->device));
+    SU2B_REQUIRE(c->nranks > 1, "mailboxes are for multi-rank runs (call su2b200_comm_init first)");
+    SU2B_REQUIRE(c->nranks <= su2b200_ctx::MBOX_MAX_RANKS, "mailbox allreduce: more ranks than mailbox entries");
+    if (!c->mbox_local) {
+      SU2B_CUDA(cudaMalloc((void**)&c->mbox_local, MBOX_WORDS * sizeof(unsigned long long)));
+      SU2B_CUDA(cudaMemset(c->mbox_local, 0, MBOX_WORDS * sizeof(unsigned long long)));
+    }
+    cudaIpcMemHandle_t h;
+    SU2B_CUDA(cudaIpcGetMemHandle(&h, c->mbox_local));
+    memcpy(handle, &h, 64);
+    return 0;
+  } catch (const std::exception& e) { set_error(e.what()); return 1; }
+}
+int su2b200_comm_mailbox_connect(su2b200_ctx* c, const unsigned char* handles) {
+  try {
+    if (!c) throw Error("null context");
+    SU2B_CUDA(cudaSetDevice(c->device));
+    SU2B_REQUIRE(c->mbox_local, "su2b200_comm_mailbox_create first");
+    std::vector<unsigned long long> table(c->nranks, 0);
+    for (int r = 0; r < c->nranks; ++r) {
+      if (r == c->rank) { c->mbox_peer_host[r] = c->mbox_local; }
+      else {
+        cudaIpcMemHandle_t h;
+        memcpy(&h, handles + (size_t)r * 64, 64);
+        void* p = nullptr;
+        const cudaError_t e = cudaIpcOpenMemHandle(&p, h, cudaIpcMemLazyEnablePeerAccess);
+        if (e != cudaSuccess) {
+          cudaGetLastError();
+          throw Error(std::string("cudaIpcOpenMemHandle failed (") + cudaGetErrorString(e) +
+                      "): the ranks must be processes on one node with peer access; NCCL allreduces stay in use");
+        }
+        c->mbox_peer_host[r] = (unsigned long long*)p;
+      }
+      table[r] = (unsigned long long)(uintptr_t)c->mbox_peer_host[r];
+    }
+    c->mbox_peers.upload(table);
+    SU2B_CUDA(cudaDeviceSynchronize());
+    static const bool enabled = !(getenv("SU2B200_MAILBOX") && atoi(getenv("SU2B200_MAILBOX")) == 0);
+    c->mbox_ready = enabled;
     return 0;
   } catch (const std::exception& e) { set_error(e.what()); return 1; }
 }

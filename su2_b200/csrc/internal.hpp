@@ -254,6 +254,12 @@ struct su2b200_ctx {
   std::vector<int> p2p_ranks, p2p_send_ptr, p2p_recv_ptr;
   su2b200::dvec<int> p2p_send_idx, p2p_recv_idx;
   su2b200::dvec<double> p2p_send_buf, p2p_recv_buf;
+  // small-message allreduce over peer memory (comm.cu): every rank owns a mailbox that its peers write into over NVLink
+  static constexpr int MBOX_MAX_RANKS = 16, MBOX_SLOTS = 4;
+  unsigned long long* mbox_local = nullptr;          // device, cudaMalloc'ed (exported through cudaIpc)
+  unsigned long long* mbox_peer_host[MBOX_MAX_RANKS] = {};
+  su2b200::dvec<unsigned long long> mbox_peers;      // device table of the nranks mailbox addresses (own one included)
+  bool mbox_ready = false;
   // overlapped exchange (e3): pack on the compute stream, send/recv + unpack on comm_stream, joined by events
   cudaEvent_t ev_packed = nullptr, ev_unpacked = nullptr;
   bool exchange_in_flight = false;

@@ -134,9 +134,40 @@ __global__ void k_mgs_stage2(int nb, const double* __restrict__ part, double* __
   }
 }
 // mode 0: nrm = w.w ; 1: first projection on v_k ; 2: second projection (if flagged) ; 3: final norm
-__global__ void k_mgs_logic(double* __restrict__ sc, int mode, int k) {
+__device__ __forceinline__ void mgs_logic(double* __restrict__ sc, int mode, int k, double prod);
+__global__ void k_mgs_logic(double* __restrict__ sc, int mode, int k) { mgs_logic(sc, mode, k, sc[6]); }
+// Multi-rank form of stage 2: block sum, allreduce through the peer mailboxes, and the scalar logic, in ONE launch
+// (instead of k_mgs_stage2 + ncclAllReduce + k_mgs_logic).  The skipped second projection skips the exchange too: the
+// flag sc[3] is the same on every rank, because every rank adds the ranks' sums in the same order.
+__global__ void __launch_bounds__(256) k_mgs_stage2_mbox(int nb, const double* __restrict__ part, double* __restrict__ sc,
+                                                         int need_flag, MailboxView mb, int mode, int k) {
+  if (need_flag && sc[3] == 0.0) {
+    if (threadIdx.x == 0) mgs_logic(sc, mode, k, 0.0);
+    return;
+  }
+  double s = 0.0;
+  for (int i = threadIdx.x; i < nb; i += blockDim.x) s += part[i];
+  __shared__ double sm[32];
+  for (int o = 16; o > 0; o >>= 1) s += __shfl_xor_sync(0xffffffffu, s, o);
+  const int wp = threadIdx.x >> 5, l = threadIdx.x & 31;
+  if (l == 0) sm[wp] = s;
+  __syncthreads();
+  if (wp == 0) {
+    s = (l < (blockDim.x >> 5)) ? sm[l] : 0.0;
+    for (int o = 16; o > 0; o >>= 1) s += __shfl_xor_sync(0xffffffffu, s, o);
+    if (l == 0) sm[0] = s;
+  }
+  __syncthreads();
+  bool timed_out = false;
+  const double total = mailbox_allreduce_block(mb, sm[0], &timed_out);
+  if (threadIdx.x == 0) {
+    sc[6] = total;
+    mgs_logic(sc, mode, k, timed_out ? __longlong_as_double(0x7ff8000000000000LL) : total);
+    if (timed_out) sc[4] = 2.0;
+  }
+}
+__device__ __forceinline__ void mgs_logic(double* __restrict__ sc, int mode, int k, double prod) {
   const double reorth = 0.98;
-  const double prod = sc[6];
   if (mode == 0) {
     sc[1] = prod; sc[2] = prod * reorth; sc[0] = 0.0; sc[3] = 0.0;
     sc[4] = ((prod <= 0.0) || (prod != prod)) ? 1.0 : 0.0;
@@ -192,9 +223,14 @@ static void mod_gram_schmidt_device(su2b200_ctx* c, LinSys& ls, int i, VecFn V, 
     {
       ProfScope prof_(c, PROF_DOT);
       SU2B_LAUNCH(c, k_mgs_dot, nb, 256, n_owned, n_all, w, vprev, vk, (const double*)sc, need_flag, part);
-      SU2B_LAUNCH(c, k_mgs_stage2, 1, 256, nb, (const double*)part, sc, need_flag);
-      allreduce_dev_sum(c, sc + 6, 1);
-      SU2B_LAUNCH(c, k_mgs_logic, 1, 1, sc, mode, k);
+      MailboxView mb;
+      if (c->nranks > 1 && mailbox_view(c, &mb)) {
+        SU2B_LAUNCH(c, k_mgs_stage2_mbox, 1, 256, nb, (const double*)part, sc, need_flag, mb, mode, k);
+      } else {
+        SU2B_LAUNCH(c, k_mgs_stage2, 1, 256, nb, (const double*)part, sc, need_flag);
+        allreduce_dev_sum(c, sc + 6, 1);
+        SU2B_LAUNCH(c, k_mgs_logic, 1, 1, sc, mode, k);
+      }
     }
   };
   dot(nullptr, nullptr, 0, 0, 0);  // nrm = w.w
@@ -209,6 +245,8 @@ static void mod_gram_schmidt_device(su2b200_ctx* c, LinSys& ls, int i, VecFn V, 
   }
   SU2B_CUDA(cudaMemcpyAsync(ls.h_mgs, sc, (size_t)(8 + i + 2) * sizeof(double), cudaMemcpyDeviceToHost, c->stream));
   SU2B_CUDA(cudaStreamSynchronize(c->stream));
+  if (ls.h_mgs[4] == 2.0)
+    throw Error("mailbox allreduce timed out: a peer rank stopped or the ranks disagree on the sequence of reductions");
   if (ls.h_mgs[4] != 0.0) throw Error("FGMRES orthogonalization failed, linear solver diverged.");
   for (int k = 0; k <= i + 1; ++k) hcol[k] = ls.h_mgs[8 + k];
 }
@@ -350,6 +388,13 @@ unsigned long linsys_solve(su2b200_ctx* c, LinSys& ls, int solver, int prec, dou
   linsys_build_prec(c, ls, prec);
   unsigned long it = 0;
   double res = 0.0;
+  // the whole Krylov workspace now: growing the pool inside the loop, the first time a solve needs one more iteration
+  // than any before it, costs two cudaMallocs + fills in the middle of a nonlinear iteration (a 10-20 ms hiccup)
+  {
+    const int mm = solver == SU2B200_SOLVER_RESTARTED_FGMRES ? std::max(1, std::min(restart, max_iter)) : max_iter;
+    const int nvec = solver == SU2B200_SOLVER_BCGSTAB ? 6 : 2 * (std::min(mm, 1000) + 1);
+    for (int k = 0; k < nvec; ++k) (void)ls.vec((size_t)k);
+  }
   // e3: inside the solve the preconditioners and products leave their trailing halo exchange to the overlapped product
   // (SU2B200_OVERLAP=0: every operator exchanges its own output in-stream, as the reference's CSysMatrixComms does)
   static const bool overlap = !(getenv("SU2B200_OVERLAP") && atoi(getenv("SU2B200_OVERLAP")) == 0);

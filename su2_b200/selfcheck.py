@@ -67,7 +67,13 @@ def run_iterations(cfg_text, n_iter, rank, world, device, comm_id=None, partitio
     s = FlowSolver(device)
     try:
         if comm_id is not None:
-            s.comm_init(rank, world, comm_id(s))
+            uid = comm_id(s)
+            allgather = None
+            if isinstance(uid, tuple):  # (NCCL id, allgather of bytes): also connect the peer-memory mailboxes
+                uid, allgather = uid
+            s.comm_init(rank, world, uid)
+            if allgather is not None and world > 1:
+                s.mailbox_connect(allgather)
         mesh.upload(s)
         z = mesh.sizes()
         P, Pd = z["nPoint"], z["nPointDomain"]

@@ -150,6 +150,15 @@ class FlowSolver:
         assert uid.size == 128
         check(self.lib.su2b200_comm_init(self.ctx, int(rank), int(size), uid.ctypes.data_as(C.POINTER(C.c_ubyte))))
 
+    def mailbox_connect(self, allgather):
+        """Peer-memory allreduce of the Krylov scalars (su2b200_comm_mailbox_*). `allgather(bytes) -> [bytes per rank]` is
+        the caller's collective (torch.distributed, MPI...). Returns False (NCCL stays in use) if the handles cannot be opened."""
+        h = (C.c_ubyte * 64)()
+        check(self.lib.su2b200_comm_mailbox_create(self.ctx, h))
+        allh = allgather(bytes(h))
+        buf = (C.c_ubyte * (64 * len(allh))).from_buffer_copy(b"".join(allh))
+        return self.lib.su2b200_comm_mailbox_connect(self.ctx, buf) == 0
+
     def halo_exchange(self, name):
         """InitiateComms/CompleteComms of a named per-point array (su2b200_halo_exchange)."""
         check(self.lib.su2b200_halo_exchange(self.ctx, capi.ARR[name]))

@@ -86,12 +86,18 @@ def whole_iterations(kind, rank, world, local):
     if su2_path:
         text = text.replace("MESH_FORMAT= BOX", "MESH_FORMAT= SU2\nMESH_FILENAME= " + su2_path)
 
+    def allgather_bytes(b):
+        t = torch.frombuffer(bytearray(b), dtype=torch.uint8).cuda()
+        out = [torch.empty_like(t) for _ in range(world)]
+        dist.all_gather(out, t)
+        return [o.cpu().numpy().tobytes() for o in out]
+
     def comm(s):
         idbuf = torch.zeros(128, dtype=torch.uint8, device="cuda")
         if rank == 0:
             idbuf.copy_(torch.from_numpy(s.comm_unique_id()).cuda())
         dist.broadcast(idbuf, 0)
-        return idbuf.cpu().numpy()
+        return idbuf.cpu().numpy(), allgather_bytes
 
     def gather(obj):
         parts = [None] * world
