@@ -55,7 +55,10 @@ static void flow_preprocessing(su2b200_ctx* c, bool output, unsigned long* nonph
   }
   if (!output) {
     s.res.zero(c->stream);
-    c->sys[0].A.zero(c->stream);
+    // Jacobian.SetValZero(): needed only where blocks are accumulated. The gather assembly OVERWRITES every block (each
+    // off-diagonal block belongs to exactly one edge, k_point_sum_rows stores the diagonal ones), so the 8.8 GB memset of
+    // the 185^3 case (1.2 ms per iteration) is left out; the coloured strategy adds into the diagonal blocks and keeps it.
+    if (cfg.assembly == SU2B200_ASSEMBLY_COLORED) c->sys[0].A.zero(c->stream);
     ++c->sys[0].A_gen;
   }
   if (!cfg.viscous) {
@@ -951,6 +954,26 @@ int su2b200_profile_report(su2b200_ctx* c, double* ms, unsigned long* calls) {
     SU2B_CUDA(cudaEventElapsedTime(&t, r.a, r.b));
     if (ms) ms[r.cat] += t;
     if (calls) calls[r.cat]++;
+  }
+  // SU2B200_PROFILE_GAPS=1: time between the end of one scope and the start of the next (records are in stream order;
+  // nested scopes give negative gaps and are skipped), summed per pair of categories, to stderr: what the categories miss
+  if (getenv("SU2B200_PROFILE_GAPS") && atoi(getenv("SU2B200_PROFILE_GAPS")) && c->prof.recs.size() > 1) {
+    std::vector<double> gap((size_t)PROF_NCAT * PROF_NCAT, 0.0);
+    std::vector<int> cnt((size_t)PROF_NCAT * PROF_NCAT, 0);
+    double total = 0.0;
+    for (size_t k = 0; k + 1 < c->prof.recs.size(); ++k) {
+      float t = 0;
+      if (cudaEventElapsedTime(&t, c->prof.recs[k].b, c->prof.recs[k + 1].a) != cudaSuccess || t <= 0.0f) continue;
+      const size_t key = (size_t)c->prof.recs[k].cat * PROF_NCAT + c->prof.recs[k + 1].cat;
+      gap[key] += t;
+      cnt[key]++;
+      total += t;
+    }
+    fprintf(stderr, "profile gaps: %.3f ms in total\n", total);
+    for (size_t key = 0; key < gap.size(); ++key)
+      if (gap[key] > 0.02)
+        fprintf(stderr, "  after %-16s before %-16s %8.3f ms in %d gaps\n", su2b200_profile_name((int)(key / PROF_NCAT)),
+                su2b200_profile_name((int)(key % PROF_NCAT)), gap[key], cnt[key]);
   }
   API_END
 }

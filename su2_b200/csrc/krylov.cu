@@ -159,7 +159,7 @@ __global__ void __launch_bounds__(256) k_mgs_stage2_mbox(int nb, const double* _
   }
   __syncthreads();
   bool timed_out = false;
-  const double total = mailbox_allreduce_block(mb, sm[0], &timed_out);
+  const double total = mb.nranks > 1 ? mailbox_allreduce_block(mb, sm[0], &timed_out) : sm[0];
   if (threadIdx.x == 0) {
     sc[6] = total;
     mgs_logic(sc, mode, k, timed_out ? __longlong_as_double(0x7ff8000000000000LL) : total);
@@ -223,8 +223,8 @@ static void mod_gram_schmidt_device(su2b200_ctx* c, LinSys& ls, int i, VecFn V, 
     {
       ProfScope prof_(c, PROF_DOT);
       SU2B_LAUNCH(c, k_mgs_dot, nb, 256, n_owned, n_all, w, vprev, vk, (const double*)sc, need_flag, part);
-      MailboxView mb;
-      if (c->nranks > 1 && mailbox_view(c, &mb)) {
+      MailboxView mb{nullptr, nullptr, 0, 1};
+      if (c->nranks <= 1 || mailbox_view(c, &mb)) {  // one rank: the same kernel without the exchange
         SU2B_LAUNCH(c, k_mgs_stage2_mbox, 1, 256, nb, (const double*)part, sc, need_flag, mb, mode, k);
       } else {
         SU2B_LAUNCH(c, k_mgs_stage2, 1, 256, nb, (const double*)part, sc, need_flag);
