@@ -7,7 +7,8 @@ from su2_b200.solver import FlowSolver
 from su2_b200.config import parse_cfg, flow_config_from_cfg, mesh_from_cfg
 n = int(sys.argv[1]); reps = int(sys.argv[2]) if len(sys.argv) > 2 else 5
 opts = parse_cfg(bench.make_cfg("RANS", [n, n, n], 1))
-mesh = mesh_from_cfg(opts); s = FlowSolver(0); mesh.upload(s)
+tets = bool(int(os.environ.get("TETS", "0")))
+mesh = mesh_from_cfg(opts, tets=tets); s = FlowSolver(0); mesh.upload(s)
 s.configure(**flow_config_from_cfg(opts, 3)); s.allocate()
 s.iterate(2)
 z = mesh.sizes()
