@@ -600,6 +600,7 @@ void flow_edge_residual(su2b200_ctx* c, unsigned long* nonphysical_edges) {
   if (c->cfg.assembly == SU2B200_ASSEMBLY_COLORED) {
     SU2B_REQUIRE(g.color_ptr.size() >= 2, "COLORED assembly needs an edge colouring");
     const int nc = (int)g.color_ptr.size() - 1;
+    ProfScope prof_(c, PROF_EDGE);
     for (int col = 0; col < nc; ++col) {
       a.color_edges = g.color_edges.p + g.color_ptr[col];
       const int n = g.color_ptr[col + 1] - g.color_ptr[col];
