@@ -716,7 +716,7 @@ int su2b200_linsys_create(su2b200_ctx* c, int which, int nVar, unsigned long nPo
   if (!c) throw Error("null context");
   SU2B_CUDA(cudaSetDevice(c->device));
   SU2B_REQUIRE(which == 0 || which == 1, "system index must be 0 or 1");
-  SU2B_REQUIRE(nVar == 1 || nVar == 4 || nVar == 5, "nVar must be 1, 4 or 5");
+  SU2B_REQUIRE(nVar == 1 || nVar == 2 || nVar == 4 || nVar == 5, "nVar must be 1, 2, 4 or 5");
   SU2B_REQUIRE(row_ptr && col_ind, "null pattern");
   auto& ls = c->sys[which];
   ls.nVar = nVar;

@@ -312,7 +312,10 @@ static bool spmv_fused_upper(su2b200_ctx* c, LinSys& ls, const double* x, double
     hp = ls.rest_halo_ptr.p;
   }
   const long warps = ((long)ls.Pd + 32 / ls.nVar - 1) / (32 / ls.nVar);
-  if (ls.nVar == 4)
+  if (ls.nVar == 2)
+    SU2B_LAUNCH(c, k_spmv_rows_rest<2>, nblk(warps * 32, 128), 128, ls.Pd, ls.row_ptr, ls.dia_ptr, hp, ls.col_ind, ls.A.p, x,
+                (const double*)ls.upper_prod.p, y);
+  else if (ls.nVar == 4)
     SU2B_LAUNCH(c, k_spmv_rows_rest<4>, nblk(warps * 32, 128), 128, ls.Pd, ls.row_ptr, ls.dia_ptr, hp, ls.col_ind, ls.A.p, x,
                 (const double*)ls.upper_prod.p, y);
   else if (ls.nVar == 5)
@@ -333,7 +336,8 @@ void linsys_spmv(su2b200_ctx* c, LinSys& ls, const double* x, double* y) {
   static const int rowsK = getenv("SU2B200_SPMV_ROWS") ? atoi(getenv("SU2B200_SPMV_ROWS")) : 1;
   if (rowsK && ls.nVar > 1) {
     const long warps = ((long)ls.Pd + 32 / ls.nVar - 1) / (32 / ls.nVar);
-    if (ls.nVar == 4) SU2B_LAUNCH(c, k_spmv_rows<4>, nblk(warps * 32, 128), 128, ls.Pd, ls.row_ptr, ls.col_ind, ls.A.p, x, y);
+    if (ls.nVar == 2) SU2B_LAUNCH(c, k_spmv_rows<2>, nblk(warps * 32, 128), 128, ls.Pd, ls.row_ptr, ls.col_ind, ls.A.p, x, y);
+    else if (ls.nVar == 4) SU2B_LAUNCH(c, k_spmv_rows<4>, nblk(warps * 32, 128), 128, ls.Pd, ls.row_ptr, ls.col_ind, ls.A.p, x, y);
     else if (ls.nVar == 5) SU2B_LAUNCH(c, k_spmv_rows<5>, nblk(warps * 32, 128), 128, ls.Pd, ls.row_ptr, ls.col_ind, ls.A.p, x, y);
     else throw Error("linsys_spmv: unsupported nVar");
     if (c->nranks > 1 && !c->defer_halo) halo_exchange(c, y, ls.nVar);
@@ -341,6 +345,7 @@ void linsys_spmv(su2b200_ctx* c, LinSys& ls, const double* x, double* y) {
   }
   switch (ls.nVar) {
     case 1: SU2B_LAUNCH(c, k_spmv_scalar, nblk((long)ls.Pd * 8, 256), 256, ls.Pd, ls.row_ptr, ls.col_ind, ls.A.p, x, y); break;
+    case 2: SU2B_LAUNCH(c, k_spmv<2>, nblk(threads, 256), 256, ls.Pd, ls.row_ptr, ls.col_ind, ls.A.p, x, y); break;
     case 4: SU2B_LAUNCH(c, k_spmv<4>, nblk(threads, 256), 256, ls.Pd, ls.row_ptr, ls.col_ind, ls.A.p, x, y); break;
     case 5: SU2B_LAUNCH(c, k_spmv<5>, nblk(threads, 256), 256, ls.Pd, ls.row_ptr, ls.col_ind, ls.A.p, x, y); break;
     default: throw Error("linsys_spmv: unsupported nVar");
@@ -405,6 +410,7 @@ void linsys_spmv_exchange_x(su2b200_ctx* c, LinSys& ls, double* x, double* y) {
     const int n = ls.n_halo_rows;
     switch (ls.nVar) {
       case 1: SU2B_LAUNCH(c, k_spmv_row_list<1>, nblk((long)n * 32, 128), 128, n, ls.halo_rows.p, ls.row_ptr, ls.col_ind, ls.A.p, x, y); break;
+      case 2: SU2B_LAUNCH(c, k_spmv_row_list<2>, nblk((long)n * 32, 128), 128, n, ls.halo_rows.p, ls.row_ptr, ls.col_ind, ls.A.p, x, y); break;
       case 4: SU2B_LAUNCH(c, k_spmv_row_list<4>, nblk((long)n * 32, 128), 128, n, ls.halo_rows.p, ls.row_ptr, ls.col_ind, ls.A.p, x, y); break;
       case 5: SU2B_LAUNCH(c, k_spmv_row_list<5>, nblk((long)n * 32, 128), 128, n, ls.halo_rows.p, ls.row_ptr, ls.col_ind, ls.A.p, x, y); break;
       default: throw Error("linsys_spmv: unsupported nVar");
@@ -512,6 +518,7 @@ void linsys_build_jacobi(su2b200_ctx* c, LinSys& ls) {
   ls.invM.alloc((size_t)ls.Pd * ls.nVar * ls.nVar);
   switch (ls.nVar) {
     case 1: SU2B_LAUNCH(c, k_jacobi_build<1>, nblk(ls.Pd, 128), 128, ls.Pd, ls.dia_ptr, ls.A.p, ls.invM.p); break;
+    case 2: SU2B_LAUNCH(c, k_jacobi_build<2>, nblk(ls.Pd, 128), 128, ls.Pd, ls.dia_ptr, ls.A.p, ls.invM.p); break;
     case 4: SU2B_LAUNCH(c, k_jacobi_build<4>, nblk(ls.Pd, 128), 128, ls.Pd, ls.dia_ptr, ls.A.p, ls.invM.p); break;
     case 5: SU2B_LAUNCH(c, k_jacobi_build<5>, nblk(ls.Pd, 128), 128, ls.Pd, ls.dia_ptr, ls.A.p, ls.invM.p); break;
     default: throw Error("jacobi: unsupported nVar");
@@ -520,6 +527,7 @@ void linsys_build_jacobi(su2b200_ctx* c, LinSys& ls) {
 void linsys_apply_jacobi(su2b200_ctx* c, LinSys& ls, const double* x, double* y) {
   switch (ls.nVar) {
     case 1: SU2B_LAUNCH(c, k_jacobi_apply<1>, nblk(ls.Pd, 128), 128, ls.Pd, ls.invM.p, x, y); break;
+    case 2: SU2B_LAUNCH(c, k_jacobi_apply<2>, nblk(ls.Pd, 128), 128, ls.Pd, ls.invM.p, x, y); break;
     case 4: SU2B_LAUNCH(c, k_jacobi_apply<4>, nblk(ls.Pd, 128), 128, ls.Pd, ls.invM.p, x, y); break;
     case 5: SU2B_LAUNCH(c, k_jacobi_apply<5>, nblk(ls.Pd, 128), 128, ls.Pd, ls.invM.p, x, y); break;
     default: throw Error("jacobi: unsupported nVar");

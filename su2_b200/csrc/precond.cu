@@ -774,6 +774,7 @@ static void ilu_apply_impl(su2b200_ctx* c, LinSys& ls, const double* x, double* 
 void linsys_build_ilu(su2b200_ctx* c, LinSys& ls) {
   switch (ls.nVar) {
     case 1: ilu_build_impl<1>(c, ls); break;
+    case 2: ilu_build_impl<2>(c, ls); break;
     case 4: ilu_build_impl<4>(c, ls); break;
     case 5: ilu_build_impl<5>(c, ls); break;
     default: throw Error("ilu: unsupported nVar");
@@ -782,6 +783,7 @@ void linsys_build_ilu(su2b200_ctx* c, LinSys& ls) {
 void linsys_apply_ilu(su2b200_ctx* c, LinSys& ls, const double* x, double* y) {
   switch (ls.nVar) {
     case 1: ilu_apply_impl<1>(c, ls, x, y); break;
+    case 2: ilu_apply_impl<2>(c, ls, x, y); break;
     case 4: ilu_apply_impl<4>(c, ls, x, y); break;
     case 5: ilu_apply_impl<5>(c, ls, x, y); break;
     default: throw Error("ilu: unsupported nVar");
@@ -810,6 +812,7 @@ void linsys_apply_lusgs(su2b200_ctx* c, LinSys& ls, const double* b, double* x) 
   SU2B_REQUIRE(b != x, "LU-SGS needs distinct input and output vectors");
   switch (ls.nVar) {
     case 1: lusgs_impl<1>(c, ls, b, x); break;
+    case 2: lusgs_impl<2>(c, ls, b, x); break;
     case 4: lusgs_impl<4>(c, ls, b, x); break;
     case 5: lusgs_impl<5>(c, ls, b, x); break;
     default: throw Error("lusgs: unsupported nVar");

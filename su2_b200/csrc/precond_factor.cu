@@ -1015,6 +1015,7 @@ static void factor_block(su2b200_ctx* c, LinSys& ls) {
 void ilu_factor_poll(su2b200_ctx* c, LinSys& ls) {
   switch (ls.nVar) {
     case 1: factor_launch_scalar(c, ls); break;
+    case 2: factor_block<2>(c, ls); break;
     case 4: factor_block<4>(c, ls); break;
     case 5: factor_block<5>(c, ls); break;
     default: throw Error("ilu_factor_poll: unsupported nVar");

@@ -865,6 +865,7 @@ void ilu_apply_poll(su2b200_ctx* c, LinSys& ls, const double* x, double* y) {
   }
   switch (ls.nVar) {
     case 1: ilu_apply_poll_impl<1>(c, ls, xin, y, ls.sweep_tmp.p); break;
+    case 2: ilu_apply_poll_impl<2>(c, ls, xin, y, ls.sweep_tmp.p); break;
     case 4: ilu_apply_poll_impl<4>(c, ls, xin, y, ls.sweep_tmp.p); break;
     case 5: ilu_apply_poll_impl<5>(c, ls, xin, y, ls.sweep_tmp.p); break;
     default: throw Error("ilu: unsupported nVar");

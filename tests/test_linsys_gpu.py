@@ -36,7 +36,7 @@ CASES = [([6, 5, 4], True), ([7, 6, 5], False)]
 
 
 @pytest.mark.parametrize("n,tets", CASES)
-@pytest.mark.parametrize("nv", [1, 4, 5])
+@pytest.mark.parametrize("nv", [1, 2, 4, 5])
 def test_spmv_ilu_and_solve_match_the_oracle(n, tets, nv):
     rng = np.random.default_rng(100 + nv + (7 if tets else 0))
     P, rp, ci, dp = _pattern(n, tets)
@@ -97,7 +97,7 @@ def test_in_place_preconditioner_application_and_repeated_builds():
 
 
 @pytest.mark.parametrize("n,tets", CASES)
-@pytest.mark.parametrize("nv", [4, 5])
+@pytest.mark.parametrize("nv", [2, 4, 5])
 @pytest.mark.parametrize("wide,mode", [(1, 1), (1, 2), (8, 1), (40, 1)])
 def test_wide_level_kernels_match_the_oracle(n, tets, nv, wide, mode):
     """The kernels that carry the benchmark -- k_poll_sweep_rows (wide-level ILU0 application) and k_factor_rows (wide-level
@@ -174,7 +174,7 @@ def test_jacobi_and_lusgs_against_the_oracle():
 
 
 @pytest.mark.parametrize("n,tets", CASES)
-@pytest.mark.parametrize("nv", [4, 5])
+@pytest.mark.parametrize("nv", [2, 4, 5])
 def test_precondition_and_multiply_equals_the_two_operators(n, tets, nv):
     """z = M^-1 v, w = A z in one call (the fused upper product on the hexahedral pattern, the plain sequence on the
     tetrahedral one, where fill-in modifies upper blocks) against ApplyPreconditioner + MatrixVectorProduct and the
