@@ -82,7 +82,10 @@ enum {
   SU2B200_ARR_STRAIN_MAG = 27,   /* CFlowVariable::StrainMag       [P]                  */
   SU2B200_ARR_WALL_DIST = 28,    /* CPoint::Wall_Distance          [P]                  */
   SU2B200_ARR_TURB_DELTA_TIME = 29,
-  SU2B200_ARR_TURB_SOLUTION_OLD = 30
+  SU2B200_ARR_TURB_SOLUTION_OLD = 30,
+  SU2B200_ARR_SST_F1 = 31,       /* CTurbSSTVariable::F1, F2, CDkw [P] each (SST only) */
+  SU2B200_ARR_SST_F2 = 32,
+  SU2B200_ARR_SST_CDKW = 33
 };
 
 /* ---- lifecycle --------------------------------------------------------------------- */
@@ -251,6 +254,13 @@ typedef struct {
   int mg_level;                      /* 0 = finest grid; > 0: agglomerated level (no MUSCL, no JST sensor/Laplacian:
                                         CEulerSolver.cpp:1584-1586, :1662; centred schemes use CLaxScheme, CNumericsSIMD.cpp:70) */
   double lax_kappa1;                 /* LAX_SENSOR_COEFF (CLaxScheme, centered.hpp:474-530): 1st-order dissipation of the coarse levels */
+  /* Menter SST, version V2003m = the reference's default (CTurbSSTSolver.cpp:40-200, option_structure.hpp:1036-1100).
+   * The turbulence arrays then hold two variables per point (k, omega): TURB_SOLUTION [P][2], TURB_GRADIENT [P][2][nDim],
+   * TURB_LINSYSRES/SOL [P][2], TURB_JACOBIAN [nnz][2][2]. */
+  int rans_sst;                      /* KIND_TURB_MODEL= SST (exclusive with rans_sa)                                  */
+  double kine_inf, omega_inf;        /* Solution_Inf: 3/2 |v_inf|^2 I^2 and rho_inf k_inf / (mu_inf ratio)             */
+  double sst_lower[2], sst_upper[2]; /* lowerlimit / upperlimit of (k, omega): 1e-10, 1e-4 / 1e10, 1e15 without DLL    */
+  double max_update_sst;             /* MAX_UPDATE_SST (1.0)                                                           */
 } su2b200_flow_config;
 
 int su2b200_flow_configure(su2b200_ctx* ctx, const su2b200_flow_config* cfg);
@@ -320,6 +330,7 @@ typedef struct {
   unsigned long linsol_iter_flow, linsol_iter_turb;
   double linsol_res_flow, linsol_res_turb;
   unsigned long nonphysical_points, nonphysical_edges;
+  double rms_turb2;            /* second turbulence variable (SST: omega); 0 for SA */
 } su2b200_iter_report;
 int su2b200_iterate(su2b200_ctx* ctx, int nIter, su2b200_iter_report* reports /*[nIter], may be NULL*/);
 

@@ -13,7 +13,7 @@ MARCH=${SU2_REF_MARCH:-x86-64-v3}
 if [ ! -d "$REF" ]; then echo "no reference tree at $REF (GPU box?) - using prebuilt $OUT"; exit 0; fi
 mkdir -p "$OUT"
 if [ -x "$OUT/SU2_CFD_b200" ] && [ -z "${SU2_SHIM_FORCE:-}" ] && [ "$OUT/SU2_CFD_b200" -nt "$HERE/CB200FlowBackend.hpp" ] \
-   && [ "$OUT/SU2_CFD_b200" -nt "$HERE/apply_patch.py" ]; then echo "integration/_ref/SU2_CFD_b200 is up to date"; exit 0; fi
+   && [ "$OUT/SU2_CFD_b200" -nt "$HERE/apply_patch.py" ] && [ "$OUT/SU2_CFD_b200" -nt "$REPO/include/su2b200.h" ]; then echo "integration/_ref/SU2_CFD_b200 is up to date"; exit 0; fi
 [ -f "$REPO/su2_b200/libsu2b200.so" ] || { echo "build su2_b200/libsu2b200.so first"; exit 1; }
 if [ ! -d "$WORK/SU2_CFD" ]; then
   mkdir -p "$WORK"

@@ -103,6 +103,11 @@ def config_from_dump(d):
     if "cfg_cfl_adapt" in d:  # fixtures made since CFL adaptation exists
         kw.update(cfl_adapt=int(d["cfg_cfl_adapt"]), n_inner_iter=int(d["cfg_n_inner_iter"]),
                   cfl_adapt_param=[float(x) for x in d["cfg_cfl_adapt_param"]])
+    if int(d.get("cfg_rans_sst", 0)):
+        assert int(d["cfg_sst_v2003"]) == 1 and int(d["cfg_sst_dll"]) == 0, "fixture made with SST options outside V2003m"
+        kw.update(rans_sst=1, kine_inf=float(d["cfg_kine_inf"]), omega_inf=float(d["cfg_omega_inf"]),
+                  max_update_sst=float(d["cfg_max_update_sst"]))
+        kw["eddy_visc_inf"] = kw["density_inf"] * kw["kine_inf"] / kw["omega_inf"]
     if kw["rans_sa"]:
         # free-stream eddy viscosity of the CTurbSASolver constructor (CTurbSASolver.cpp:100-134)
         t = kw["temperature_inf"]

@@ -40,6 +40,9 @@ CASES = {
     "rect_rans_sa": ("rect_rans_sa.cfg", 6, "0,1,2", 2, None),              # 2-D RANS-SA (config 3's shape)
     "box_tet_roe": ("box_tet_roe.cfg", 6, "0,1,2", 2, "gen:tetbox"),         # 3-D tetrahedra through the flow kernels
     "wingbox_rans_sa": ("wingbox_rans_sa.cfg", 6, "0,1,2", 2, "gen:wingbox"),  # stretched wall-normal spacing
+    # Menter SST (V2003m): two-variable turbulence system, k in the flow's static energy
+    "box_rans_sst": ("box_rans_sst.cfg", 6, "0,1,2", 2, None),
+    "rect_rans_sst": ("rect_rans_sst.cfg", 6, "0,1,2", 2, None),
     # FAS multigrid: C1 as shipped (3 coarse levels, W-cycle); agglomerated levels + every transfer step of iteration 0
     "naca0012_mg": ("naca0012_mg.cfg", 30, "0", None, "mesh_NACA0012_inv.su2"),
 }

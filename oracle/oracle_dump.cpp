@@ -45,6 +45,7 @@
 #include "SU2_CFD/include/solvers/CEulerSolver.hpp"
 #include "SU2_CFD/include/solvers/CNSSolver.hpp"
 #include "SU2_CFD/include/solvers/CTurbSASolver.hpp"
+#include "SU2_CFD/include/solvers/CTurbSSTSolver.hpp"
 #include "SU2_CFD/include/integration/CIntegration.hpp"
 #include "SU2_CFD/include/integration/CMultiGridIntegration.hpp"
 #include "SU2_CFD/include/variables/CEulerVariable.hpp"
@@ -182,6 +183,16 @@ class Dumper : public CSinglezoneDriver {
     w.scalar("cfg_gamma", c->GetGamma()); w.scalar("cfg_gas_constant", c->GetGas_ConstantND());
     w.iscalar("cfg_viscous", c->GetViscous());
     w.iscalar("cfg_rans_sa", c->GetKind_Turb_Model() == TURB_MODEL::SA);
+    w.iscalar("cfg_rans_sst", c->GetKind_Turb_Model() == TURB_MODEL::SST);
+    if (c->GetKind_Turb_Model() == TURB_MODEL::SST) {
+      auto* tsol = solver_container[ZONE_0][INST_0][MESH_0][TURB_SOL];
+      w.iscalar("cfg_turb_reducer", static_cast<CTurbSSTSolver*>(tsol)->ReducerStrategy);
+      w.scalar("cfg_kine_inf", tsol->GetTke_Inf());
+      w.scalar("cfg_omega_inf", tsol->GetOmega_Inf());
+      w.scalar("cfg_max_update_sst", c->GetMaxUpdateFractionSST());
+      w.iscalar("cfg_sst_v2003", c->GetSSTParsedOptions().version == SST_OPTIONS::V2003);
+      w.iscalar("cfg_sst_dll", c->GetSSTParsedOptions().dll);
+    }
     w.iscalar("cfg_sa_negative", c->GetSAParsedOptions().version == SA_OPTIONS::NEG);
     if (c->GetKind_Turb_Model() == TURB_MODEL::SA)  // averaged SA diffusion Jacobians (CScalarSolver.inl:59)
       w.iscalar("cfg_turb_reducer", static_cast<CTurbSASolver*>(solver_container[ZONE_0][INST_0][MESH_0][TURB_SOL])->ReducerStrategy);
@@ -483,7 +494,7 @@ class Dumper : public CSinglezoneDriver {
       flow->Pressure_Forces(g, config);
       flow->Momentum_Forces(g, config);
       flow->Friction_Forces(g, config);
-      double rms_turb = 0.0;
+      double rms_turb = 0.0, rms_turb2 = 0.0;
       long turb_iter = 0;
       double turb_linres = 0.0;
       if (rans) {
@@ -492,9 +503,21 @@ class Dumper : public CSinglezoneDriver {
         const std::string tp = pre + "turb_";
         config->SetGlobalParam(config->GetKind_Solver(), RUNTIME_TURB_SYS);  // CFluidIteration.cpp:96
         turb->Preprocessing(g, solvers, config, MESH_0, 0, RUNTIME_TURB_SYS, false);
+        const unsigned long tv = turb->GetnVar();
+        auto dump_sst = [&](const std::string& name) {
+          if (tv != 2) return;
+          std::vector<double> f1(P), f2(P), cd(P), mut(P);
+          for (unsigned long i = 0; i < P; ++i) {
+            f1[i] = turb->GetNodes()->GetF1blending(i); f2[i] = turb->GetNodes()->GetF2blending(i);
+            cd[i] = turb->GetNodes()->GetCrossDiff(i); mut[i] = turb->GetNodes()->GetmuT(i);
+          }
+          w.f64(name + "F1", {P}, f1.data()); w.f64(name + "F2", {P}, f2.data());
+          w.f64(name + "CDkw", {P}, cd.data()); w.f64(name + "mut", {P}, mut.data());
+        };
         if (D) {
-          dump_matrix(w, tp + "pre_solution", turb->GetNodes()->GetSolution(), P, 1);
-          dump_grad(w, tp + "pre_gradient", turb->GetNodes()->GetGradient(), P, 1, g->GetnDim());
+          dump_matrix(w, tp + "pre_solution", turb->GetNodes()->GetSolution(), P, tv);
+          dump_grad(w, tp + "pre_gradient", turb->GetNodes()->GetGradient(), P, tv, g->GetnDim());
+          dump_sst(tp + "pre_");
           DumpFlowState(w, pre + "flowout_");
         }
         turb->Set_OldSolution();
@@ -524,13 +547,16 @@ class Dumper : public CSinglezoneDriver {
         turb->ImplicitEuler_Iteration(g, solvers, config);
         turb->Postprocessing(g, solvers, config, MESH_0);
         if (D) {
-          dump_sysvec(w, tp + "linsyssol", turb->LinSysSol, P, 1);
-          dump_matrix(w, tp + "post_solution", turb->GetNodes()->GetSolution(), P, 1);
+          dump_sysvec(w, tp + "linsyssol", turb->LinSysSol, P, tv);
+          dump_matrix(w, tp + "post_solution", turb->GetNodes()->GetSolution(), P, tv);
+          dump_sst(tp + "post_");
+          dump_grad(w, tp + "post_gradient", turb->GetNodes()->GetGradient(), P, tv, g->GetnDim());
           std::vector<double> mut(P);
           for (unsigned long i = 0; i < P; ++i) mut[i] = turb->GetNodes()->GetmuT(i);
           w.f64(tp + "post_mut", {P}, mut.data());
         }
         rms_turb = turb->GetRes_RMS(0);
+        if (tv > 1) rms_turb2 = turb->GetRes_RMS(1);
         turb_iter = turb->GetIterLinSolver();
         turb_linres = turb->GetResLinSolver();
       }
@@ -547,9 +573,10 @@ class Dumper : public CSinglezoneDriver {
       hist.push_back(flow->GetTotal_CL()); hist.push_back(flow->GetTotal_CD());
       hist.push_back((double)flow->GetIterLinSolver()); hist.push_back(flow->GetResLinSolver());
       hist.push_back((double)turb_iter); hist.push_back(turb_linres);
+      hist.push_back(rms_turb2);  // second turbulence variable (SST: omega), 0 otherwise
       fprintf(stderr, "[oracle_dump] it %d rms0 %.9e CL %.9f CD %.9f linit %lu\n", it, flow->GetRes_RMS(0), flow->GetTotal_CL(), flow->GetTotal_CD(), flow->GetIterLinSolver());
     }
-    w.f64("history", {(unsigned long)nIter, 12}, hist.data());
+    w.f64("history", {(unsigned long)nIter, 13}, hist.data());
     dump_matrix(w, "final_solution", flow->nodes->GetSolution(), P, nVar);
   }
 };

@@ -56,6 +56,8 @@ class FlowConfig(C.Structure):
         ("assembly", C.c_int), ("prec_partitions", C.c_int), ("turb_reducer", C.c_int),
         ("cfl_adapt", C.c_int), ("cfl_adapt_param", C.c_double * 6), ("n_inner_iter", C.c_ulong),
         ("mg_level", C.c_int), ("lax_kappa1", C.c_double),
+        ("rans_sst", C.c_int), ("kine_inf", C.c_double), ("omega_inf", C.c_double),
+        ("sst_lower", C.c_double * 2), ("sst_upper", C.c_double * 2), ("max_update_sst", C.c_double),
     ]
 
 
@@ -71,7 +73,7 @@ class IterReport(C.Structure):
         ("rms_flow", C.c_double * 5), ("rms_turb", C.c_double), ("CL", C.c_double), ("CD", C.c_double),
         ("linsol_iter_flow", C.c_ulong), ("linsol_iter_turb", C.c_ulong),
         ("linsol_res_flow", C.c_double), ("linsol_res_turb", C.c_double),
-        ("nonphysical_points", C.c_ulong), ("nonphysical_edges", C.c_ulong),
+        ("nonphysical_points", C.c_ulong), ("nonphysical_edges", C.c_ulong), ("rms_turb2", C.c_double),
     ]
 
 
@@ -89,7 +91,7 @@ ARR = dict(
     LINSYSSOL=8, JACOBIAN=9, LAMBDA=10, SENSOR=11, UND_LAPL=12, MAX_LAMBDA_INV=13, MAX_LAMBDA_VISC=14, ILU=15,
     INVM=16, UNDER_RELAX=17, RES_TRUNC=18, LOCAL_CFL=19, TURB_SOLUTION=20, TURB_GRADIENT=21, TURB_LINSYSRES=22, TURB_LINSYSSOL=23,
     TURB_JACOBIAN=24, EDDY_VISC=25, VORTICITY=26, STRAIN_MAG=27, WALL_DIST=28, TURB_DELTA_TIME=29,
-    TURB_SOLUTION_OLD=30)
+    TURB_SOLUTION_OLD=30, SST_F1=31, SST_F2=32, SST_CDKW=33)
 
 # every symbol include/su2b200.h declares (tests check that the library exports all of them)
 EXPORTED_SYMBOLS = [

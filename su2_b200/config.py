@@ -23,7 +23,8 @@ _DEFAULTS = {
     "SLOPE_LIMITER_FLOW": "VENKATAKRISHNAN", "VENKAT_LIMITER_COEFF": "0.05", "JST_SENSOR_COEFF": "( 0.5, 0.02 )",
     "ROE_KAPPA": "0.5", "ENTROPY_FIX_COEFF": "0.001", "CENTRAL_JACOBIAN_FIX_FACTOR": "4.0",
     "LINEAR_SOLVER": "FGMRES", "LINEAR_SOLVER_PREC": "ILU", "LINEAR_SOLVER_ERROR": "1E-6", "LINEAR_SOLVER_ITER": "10",
-    "LINEAR_SOLVER_RESTART_FREQUENCY": "10", "MAX_UPDATE_FLOW": "0.2", "MAX_UPDATE_SA": "0.99",
+    "LINEAR_SOLVER_RESTART_FREQUENCY": "10", "MAX_UPDATE_FLOW": "0.2", "MAX_UPDATE_SA": "0.99", "MAX_UPDATE_SST": "1.0",
+    "SST_OPTIONS": "NONE", "FREESTREAM_TURBULENCEINTENSITY": "0.05", "FREESTREAM_TURB2LAMVISCRATIO": "10.0",
     "TIME_DISCRE_FLOW": "EULER_IMPLICIT", "MGLEVEL": "0", "SA_OPTIONS": "NONE", "MESH_FORMAT": "SU2",
     "MESH_FILENAME": "mesh.su2", "MESH_BOX_SIZE": "33, 33, 33", "MESH_BOX_LENGTH": "1.0, 1.0, 1.0",
     "MESH_BOX_OFFSET": "0.0, 0.0, 0.0", "ITER": "1", "CFL_ADAPT": "NO", "CFL_ADAPT_PARAM": "",
@@ -81,8 +82,12 @@ def flow_config_from_cfg(opts, nDim):
     viscous = solver != "EULER"
     rans = solver == "RANS"
     turb = o["KIND_TURB_MODEL"].upper()
-    if rans and turb != "SA":
-        raise ValueError("KIND_TURB_MODEL= %s not supported (SA only)" % turb)
+    if rans and turb not in ("SA", "SST"):
+        raise ValueError("KIND_TURB_MODEL= %s not supported (SA, SST)" % turb)
+    sst = rans and turb == "SST"
+    if sst and o["SST_OPTIONS"].upper() not in ("NONE", "V2003M"):
+        raise ValueError("SST_OPTIONS= %s not supported (the default V2003m only)" % o["SST_OPTIONS"])
+    rans = rans and not sst  # `rans` below means the SA model
     if o["TIME_DISCRE_FLOW"].upper() != "EULER_IMPLICIT":
         raise ValueError("only TIME_DISCRE_FLOW= EULER_IMPLICIT is on the path")
     if int(o["MGLEVEL"]) != 0:
@@ -137,6 +142,15 @@ def flow_config_from_cfg(opts, nDim):
         chi = nu_tilde / (mu_inf_nd / rho_nd)
         fv1 = chi ** 3 / (chi ** 3 + 7.1 ** 3)
         eddy = rho_nd * fv1 * nu_tilde
+    kine_inf = omega_inf = 0.0
+    if sst:
+        # CTurbSSTSolver ctor (CTurbSSTSolver.cpp:118-131): k = 3/2 |v|^2 I^2, omega = rho k / (mu ratio); muT = rho k / omega
+        inten, ratio = float(o["FREESTREAM_TURBULENCEINTENSITY"]), float(o["FREESTREAM_TURB2LAMVISCRATIO"])
+        vel2 = sum(v * v for v in vel_nd[:nDim])
+        kine_inf = 3.0 / 2.0 * (vel2 * inten * inten)
+        omega_inf = rho_nd * kine_inf / (mu_inf_nd * ratio)
+        eddy = rho_nd * kine_inf / omega_inf
+        energy_nd += kine_inf  # if (tkeNeeded) Energy_FreeStreamND += Tke_FreeStreamND (CEulerSolver.cpp:1153)
     grad = {"GREEN_GAUSS": capi.GRAD_GREEN_GAUSS, "LEAST_SQUARES": capi.GRAD_LEAST_SQUARES,
             "WEIGHTED_LEAST_SQUARES": capi.GRAD_WEIGHTED_LEAST_SQUARES}
     gm = grad[o["NUM_METHOD_GRAD"].upper()]
@@ -160,7 +174,8 @@ def flow_config_from_cfg(opts, nDim):
         mu_ref=mu_ref / visc_ref, mu_temperature_ref=mu_tref / t_ref, mu_sutherland=mu_s / t_ref,
         mu_constant=mu_ref / visc_ref, prandtl_lam=float(o["PRANDTL_LAM"]), prandtl_turb=float(o["PRANDTL_TURB"]),
         density_inf=rho_nd, pressure_inf=p_nd, velocity_inf=vel_nd, energy_inf=energy_nd, temperature_inf=t_nd,
-        nu_tilde_inf=nu_tilde, eddy_visc_inf=eddy,
+        nu_tilde_inf=nu_tilde, eddy_visc_inf=eddy, rans_sst=int(sst), kine_inf=kine_inf, omega_inf=omega_inf,
+        max_update_sst=float(o["MAX_UPDATE_SST"]),
         conv_scheme=capi.CONV_JST if conv == "JST" else capi.CONV_ROE,
         muscl=muscl, muscl_kappa=float(o["MUSCL_KAPPA_FLOW"]), limiter=lim,
         venkat_coeff=float(o["VENKAT_LIMITER_COEFF"]),

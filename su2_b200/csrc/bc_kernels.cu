@@ -12,6 +12,7 @@ FlowParams flow_params(const su2b200_ctx* c);
 
 struct FarFieldInf {
   double rho, p, vel[3];
+  double tke;  // GetTke_Inf() with SST (tkeNeeded, CEulerSolver.cpp:4801, :4951), else 0
 };
 
 // CEulerSolver::BC_Far_Field (CEulerSolver.cpp:4780-5034): Riemann-invariant far-field state, then the
@@ -75,7 +76,8 @@ __global__ void k_bc_far_field(int nV, int Pd, FlowParams p, FarFieldInf inf, co
 #pragma unroll
   for (int d = 0; d < ND; ++d) v2 += vel[d] * vel[d];
   const double pres = rho * c * c / gamma;
-  const double energy = pres / (gm1 * rho) + 0.5 * v2;
+  double energy = pres / (gm1 * rho) + 0.5 * v2;
+  energy += inf.tke;  // if (tkeNeeded) Energy += GetTke_Inf(); x + 0.0 == x otherwise
 
   double* Vinf = charac + (size_t)t * I::NPRIM;  // persistent CharacPrimVar: entries not set here keep their value
   double Vj[I::NPRIM];
@@ -257,6 +259,7 @@ void flow_bc_far_field(su2b200_ctx* c, int iMarker) {
   FarFieldInf inf;
   inf.rho = c->cfg.density_inf;
   inf.p = c->cfg.pressure_inf;
+  inf.tke = c->cfg.rans_sst ? c->cfg.kine_inf : 0.0;
   for (int d = 0; d < 3; ++d) inf.vel[d] = c->cfg.velocity_inf[d];
   const int nb = nblk(m.nVertex, 64);
   double* A = c->sys[0].A.p;

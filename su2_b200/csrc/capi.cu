@@ -405,7 +405,29 @@ int su2b200_flow_allocate(su2b200_ctx* c) {
   }
   s.U.upload(U);
   s.U_old.upload(U);
+  SU2B_REQUIRE(!(c->cfg.rans_sa && c->cfg.rans_sst), "one turbulence model at a time");
+  if (c->cfg.rans_sst) {
+    // CTurbSSTSolver ctor (CTurbSSTSolver.cpp:118-150): (k, omega) = Solution_Inf, muT = rho k / omega everywhere
+    SU2B_REQUIRE(c->cfg.viscous, "SST needs the viscous flow solver");
+    s.nTurb = 2;
+    alloc0(s.nu_old, (size_t)P * 2);
+    alloc0(s.nu_grad, (size_t)P * 2 * nd);
+    alloc0(s.turb_res, (size_t)P * 2);
+    alloc0(s.turb_sol, (size_t)P * 2);
+    alloc0(s.turb_dt, P);
+    alloc0(s.turb_under_relax, P);
+    alloc0(s.sst_F1, P);
+    alloc0(s.sst_F2, P);
+    alloc0(s.sst_CDkw, P);
+    std::vector<double> tk((size_t)P * 2), mut(P, c->cfg.density_inf * c->cfg.kine_inf / c->cfg.omega_inf);
+    for (int i = 0; i < P; ++i) { tk[(size_t)2 * i] = c->cfg.kine_inf; tk[(size_t)2 * i + 1] = c->cfg.omega_inf; }
+    s.nu.upload(tk);
+    s.nu_old.upload(tk);
+    s.mu_t.upload(mut);
+    linsys_bind(c, 1, 2);
+  }
   if (c->cfg.rans_sa) {
+    s.nTurb = 1;
     alloc0(s.nu_old, P);
     alloc0(s.nu_grad, (size_t)P * nd);
     alloc0(s.turb_res, P);
@@ -421,6 +443,13 @@ int su2b200_flow_allocate(su2b200_ctx* c) {
   }
   SU2B_CUDA(cudaDeviceSynchronize());
   s.allocated = true;
+  if (c->cfg.rans_sst) {
+    // the driver's solver preprocessing runs CTurbSSTSolver::Postprocessing once on the initial state: F1, F2, CDkw and
+    // the limited muT of the free stream (zero gradients, zero strain)
+    flow_primitives(c);
+    turb_postprocessing(c);
+    SU2B_CUDA(cudaDeviceSynchronize());
+  }
   API_END
 }
 
@@ -459,6 +488,9 @@ static bool locate_array(su2b200_ctx* c, int which, double** p, size_t* n) {
     case SU2B200_ARR_VORTICITY: return set(s.vorticity);
     case SU2B200_ARR_STRAIN_MAG: return set(s.strain_mag);
     case SU2B200_ARR_WALL_DIST: return set(c->geo.wall_dist);
+    case SU2B200_ARR_SST_F1: return set(s.sst_F1);
+    case SU2B200_ARR_SST_F2: return set(s.sst_F2);
+    case SU2B200_ARR_SST_CDKW: return set(s.sst_CDkw);
     default: return false;
   }
 }

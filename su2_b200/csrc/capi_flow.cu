@@ -223,10 +223,11 @@ int su2b200_turb_space_integration(su2b200_ctx* c) {
 int su2b200_turb_prepare_implicit(su2b200_ctx* c, double* rms, double* mx, unsigned long* idx) {
   API_BEGIN
   require_flow(c);
-  double r = 0.0;
-  turb_prepare_implicit_generic(c, &r, mx, idx);
-  c->fs.last_rms_turb = r;
-  if (rms) *rms = r;
+  double r[2] = {0.0, 0.0};  // rms/mx/idx: [1] for SA, [2] for SST
+  turb_prepare_implicit_generic(c, r, mx, idx);
+  c->fs.last_rms_turb = r[0];
+  c->fs.last_rms_turb2 = r[1];
+  if (rms) for (int v = 0; v < c->fs.nTurb; ++v) rms[v] = r[v];
   API_END
 }
 int su2b200_turb_linear_solve(su2b200_ctx* c, unsigned long* iterations, double* residual) {
@@ -288,14 +289,15 @@ int su2b200_iterate(su2b200_ctx* c, int nIter, su2b200_iter_report* reports) {
     rep.linsol_res_flow = c->lin_res[0];
     rep.nonphysical_points = np;
     rep.nonphysical_edges = ne;
-    if (c->cfg.rans_sa) {
+    if (c->cfg.rans_sa || c->cfg.rans_sst) {
       // CSingleGridIntegration::SingleGrid_Iteration (CSingleGridIntegration.cpp:40-105)
       turb_preprocessing(c);
       vec_copy(c, s.nu.n, s.nu.p, s.nu_old.p);
       turb_set_time_step(c);
       turb_space_integration(c);
-      double trms = 0;
-      turb_prepare_implicit_generic(c, &trms, nullptr, nullptr);
+      double trms2[2] = {0.0, 0.0};
+      turb_prepare_implicit_generic(c, trms2, nullptr, nullptr);
+      const double trms = trms2[0];
       const auto& cfg = c->cfg;
       double res = 0.0;
       c->lin_iters[1] = linsys_solve(c, c->sys[1], cfg.turb_linear_solver, cfg.turb_linear_prec, cfg.turb_linear_tol,
@@ -304,6 +306,8 @@ int su2b200_iterate(su2b200_ctx* c, int nIter, su2b200_iter_report* reports) {
       turb_complete_implicit(c);
       turb_postprocessing(c);
       rep.rms_turb = trms;
+      rep.rms_turb2 = trms2[1];
+      s.last_rms_turb2 = trms2[1];
       rep.linsol_iter_turb = c->lin_iters[1];
       rep.linsol_res_turb = res;
       s.last_rms_turb = trms;

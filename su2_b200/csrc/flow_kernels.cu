@@ -21,7 +21,7 @@ struct PrimParams {
 };
 
 template <int ND>
-__device__ __forceinline__ bool prim_from_cons(const PrimParams& pp, const double* U, double* V) {
+__device__ __forceinline__ bool prim_from_cons(const PrimParams& pp, const double* U, double* V, double tke = 0.0) {
   using I = PrimIdx<ND>;
   constexpr int NV = ND + 2;
   double vel2 = 0.0;
@@ -31,7 +31,8 @@ __device__ __forceinline__ bool prim_from_cons(const PrimParams& pp, const doubl
     vel2 += V[I::VEL + d] * V[I::VEL + d];
   }
   const double rho = U[0];
-  const double e = U[NV - 1] / U[0] - 0.5 * vel2;
+  // CNSVariable::SetPrimVar: staticEnergy = E - 0.5 v^2 - turb_ke (SST only; x - 0.0 == x otherwise)
+  const double e = U[NV - 1] / U[0] - 0.5 * vel2 - tke;
   const double pres = pp.gm1 * rho * e;
   const double temp = pp.gm1 * e / pp.R;
   const double c2 = pp.gamma * pres / rho;
@@ -45,7 +46,7 @@ __device__ __forceinline__ bool prim_from_cons(const PrimParams& pp, const doubl
 
 template <int ND>
 __global__ void k_primitives(int P, PrimParams pp, double* __restrict__ U, const double* __restrict__ U_old,
-                             const double* __restrict__ mu_t, double* __restrict__ V,
+                             const double* __restrict__ mu_t, const double* __restrict__ tk, double* __restrict__ V,
                              unsigned long long* __restrict__ nonphys) {
   using I = PrimIdx<ND>;
   constexpr int NV = ND + 2;
@@ -56,14 +57,15 @@ __global__ void k_primitives(int P, PrimParams pp, double* __restrict__ U, const
   for (int k = 0; k < NV; ++k) u[k] = U[(size_t)i * NV + k];
 #pragma unroll
   for (int k = 0; k < I::NPRIM; ++k) v[k] = V[(size_t)i * I::NPRIM + k];  // sound speed keeps old value if c2<0
-  bool bad = prim_from_cons<ND>(pp, u, v);
+  const double tke = tk ? tk[(size_t)2 * i] : 0.0;  // CNSSolver.cpp:135-158: tkeNeeded = SST
+  bool bad = prim_from_cons<ND>(pp, u, v, tke);
   if (bad) {
 #pragma unroll
     for (int k = 0; k < NV; ++k) {
       u[k] = U_old[(size_t)i * NV + k];
       U[(size_t)i * NV + k] = u[k];
     }
-    prim_from_cons<ND>(pp, u, v);
+    prim_from_cons<ND>(pp, u, v, tke);
     atomicAdd(nonphys, 1ull);
   }
   v[I::H] = (u[NV - 1] + v[I::P]) / u[0];
@@ -744,10 +746,11 @@ void flow_primitives(su2b200_ctx* c) {
   auto& g = c->geo;
   auto& s = c->fs;
   const PrimParams pp = make_prim_params(c->cfg);
-  const double* mut = (c->cfg.viscous && c->cfg.rans_sa) ? s.mu_t.p : nullptr;
+  const double* mut = (c->cfg.viscous && (c->cfg.rans_sa || c->cfg.rans_sst)) ? s.mu_t.p : nullptr;
+  const double* tk = (c->cfg.viscous && c->cfg.rans_sst) ? s.nu.p : nullptr;
   SU2B_CUDA(cudaMemsetAsync(s.counters.p, 0, sizeof(unsigned long long), c->stream));
-  if (g.nDim == 2) LAUNCH(c, k_primitives<2>, nblk(g.P, 256), 256, g.P, pp, s.U.p, s.U_old.p, mut, s.V.p, s.counters.p);
-  else LAUNCH(c, k_primitives<3>, nblk(g.P, 256), 256, g.P, pp, s.U.p, s.U_old.p, mut, s.V.p, s.counters.p);
+  if (g.nDim == 2) LAUNCH(c, k_primitives<2>, nblk(g.P, 256), 256, g.P, pp, s.U.p, s.U_old.p, mut, tk, s.V.p, s.counters.p);
+  else LAUNCH(c, k_primitives<3>, nblk(g.P, 256), 256, g.P, pp, s.U.p, s.U_old.p, mut, tk, s.V.p, s.counters.p);
 }
 
 // field = primitives (first NG = nDim+2 or nDim+1 variables); `into` selects the gradient array.
@@ -836,6 +839,49 @@ void scalar_gradient(su2b200_ctx* c, int method, const double* field, double* gr
   ProfScope prof_(c, PROF_GRADIENT);
   if (c->geo.nDim == 2) scalar_gradient_impl<2>(c, method, field, grad);
   else scalar_gradient_impl<3>(c, method, field, grad);
+}
+
+// the same for a two-variable field [P][2] -> [P][2][ND] (SST: k, omega)
+template <int ND>
+__global__ void k_grad_sym_scalar2(int nV, const int* __restrict__ vnode, const double* __restrict__ unit,
+                                   double* __restrict__ grad) {
+  const int t = blockIdx.x * blockDim.x + threadIdx.x;
+  if (t >= nV) return;
+  const int i = vnode[t];
+#pragma unroll
+  for (int v = 0; v < 2; ++v) {
+    double* gv = grad + ((size_t)i * 2 + v) * ND;
+    double ng = 0.0;
+#pragma unroll
+    for (int d = 0; d < ND; ++d) ng += unit[(size_t)t * ND + d] * gv[d];
+#pragma unroll
+    for (int d = 0; d < ND; ++d) gv[d] -= ng * unit[(size_t)t * ND + d];
+  }
+}
+template <int ND>
+static void scalar2_gradient_impl(su2b200_ctx* c, int method, const double* field, double* grad) {
+  auto& g = c->geo;
+  if (method == SU2B200_GRAD_GREEN_GAUSS) {
+    LAUNCH(c, (k_grad_gg<ND, 2>), nblk(g.Pd, 128), 128, g.Pd, 2, 2, g.nbr_ptr.p, g.nbr_pt.p, g.nbr_edge.p,
+           g.edge_normal.p, g.E, g.volume.p, field, grad);
+    for (auto& m : g.markers) {
+      if (m.kind == SU2B200_SEND_RECEIVE || m.nVertex == 0) continue;
+      LAUNCH(c, (k_grad_gg_bnd<ND, 2>), nblk(m.nVertex, 128), 128, m.nVertex, g.Pd, 2, 2, m.node.p, m.normal.p,
+             g.volume.p, field, grad);
+    }
+  } else {
+    const int weighted = (method == SU2B200_GRAD_WEIGHTED_LEAST_SQUARES);
+    LAUNCH(c, (k_grad_ls<ND, 2>), nblk(g.Pd, 128), 128, g.Pd, 2, 2, weighted, g.nbr_ptr.p, g.nbr_pt.p, g.coord.p, field,
+           grad);
+  }
+  for (auto& m : g.markers)
+    if ((m.kind == SU2B200_SYMMETRY_PLANE || m.kind == SU2B200_EULER_WALL) && m.nVertex > 0)
+      LAUNCH(c, k_grad_sym_scalar2<ND>, nblk(m.nVertex, 128), 128, m.nVertex, m.node.p, m.unit_sym.p, grad);
+}
+void scalar2_gradient(su2b200_ctx* c, int method, const double* field, double* grad) {
+  ProfScope prof_(c, PROF_GRADIENT);
+  if (c->geo.nDim == 2) scalar2_gradient_impl<2>(c, method, field, grad);
+  else scalar2_gradient_impl<3>(c, method, field, grad);
 }
 
 void flow_limiter(su2b200_ctx* c) {
@@ -943,7 +989,7 @@ void flow_adapt_cfl(su2b200_ctx* c, unsigned long inner_iter, double* out_min, d
   const double fdec = cfg.cfl_adapt_param[0], finc = cfg.cfl_adapt_param[1], cmin = cfg.cfl_adapt_param[2],
                cmax = cfg.cfl_adapt_param[3], acceptable = cfg.cfl_adapt_param[4], starting = cfg.cfl_adapt_param[5];
   const unsigned long res_count = std::min(100ul, cfg.n_inner_iter > 0 ? cfg.n_inner_iter - 1 : 0ul);
-  const bool rans = cfg.rans_sa != 0;
+  const bool rans = cfg.rans_sa != 0 || cfg.rans_sst != 0;
   const double linRes = std::max(c->lin_res[0], rans ? c->lin_res[1] : 0.0);
   const double linTol = std::max(acceptable, cfg.linear_tol);
   bool reset = linRes > 0.99;
@@ -956,6 +1002,7 @@ void flow_adapt_cfl(su2b200_ctx* c, unsigned long inner_iter, double* out_min, d
     int total = 0;
     for (int v = 0; v < s.nVar; ++v) { f += std::log10(s.last_rms[v]); ++total; }
     if (rans) { f += std::log10(s.last_rms_turb); ++total; }
+    if (cfg.rans_sst) { f += std::log10(s.last_rms_turb2); ++total; }
     s.adapt_new_func = f / total;
     if (inner_iter == 1 && s.adapt_new_func - s.adapt_old_func > 10) s.adapt_old_func = s.adapt_new_func;
     s.adapt_series[s.adapt_counter] = s.adapt_new_func - s.adapt_old_func;
@@ -1091,7 +1138,8 @@ void flow_prepare_implicit(su2b200_ctx* c, double* rms, double* mx, unsigned lon
 void turb_prepare_implicit_generic(su2b200_ctx* c, double* rms, double* mx, unsigned long* idx) {
   ProfScope prof_(c, PROF_PREPARE);
   auto& s = c->fs;
-  prepare_implicit_impl<1>(c, c->sys[1], s.turb_dt.p, s.turb_res.p, s.turb_sol.p, nullptr, rms, mx, idx);
+  if (s.nTurb == 2) prepare_implicit_impl<2>(c, c->sys[1], s.turb_dt.p, s.turb_res.p, s.turb_sol.p, nullptr, rms, mx, idx);
+  else prepare_implicit_impl<1>(c, c->sys[1], s.turb_dt.p, s.turb_res.p, s.turb_sol.p, nullptr, rms, mx, idx);
 }
 
 void flow_complete_implicit(su2b200_ctx* c) {

@@ -88,6 +88,7 @@ struct Marker {
   dvec<int> normal_nbr;    // [nV]
   dvec<double> unit_sym;   // [nV][nDim] unit normal used by symmetry/Euler-wall treatment
   dvec<double> charac;     // [nV][nDim+9] CharacPrimVar (CFVMFlowSolverBase.hpp:176), zero-initialised
+  dvec<double> nn_dist;    // [nV] CVertex::NearestNeighborDistance of viscous walls (SST wall omega; built on first use)
 };
 
 struct Geometry {
@@ -211,6 +212,9 @@ struct FlowState {
   dvec<double> vorticity, strain_mag;
   // turbulence (SA)
   dvec<double> nu, nu_old, nu_grad, mu_t, turb_res, turb_sol, turb_dt, turb_under_relax, turb_edge_flux;
+  double last_rms_turb2 = 0.0;
+  int nTurb = 1;                             // variables of the turbulence model: 1 (SA: nu_tilde), 2 (SST: k, omega)
+  dvec<double> sst_F1, sst_F2, sst_CDkw;     // CTurbSSTVariable blending functions and cross diffusion [P]
   dvec<unsigned long long> counters;         // device counters (non-physical points/edges)
   dvec<double> red;                          // reduction scratch
   double* h_red = nullptr;                   // pinned

@@ -8,6 +8,7 @@ namespace su2b200 {
 void flow_primitives(su2b200_ctx* c);
 void flow_gradient(su2b200_ctx* c, int reconstruction, int nvars);
 void flow_limiter(su2b200_ctx* c);
+void scalar2_gradient(su2b200_ctx* c, int method, const double* field, double* grad);  // [P][2] -> [P][2][nDim]
 void scalar_gradient(su2b200_ctx* c, int method, const double* field, double* grad);
 void flow_time_step(su2b200_ctx* c);
 void flow_jst_preprocess(su2b200_ctx* c);

@@ -226,6 +226,7 @@ int su2b200_restart_write(su2b200_ctx* c, const char* path, int binary, const un
   const int nd = g.nDim;
   std::vector<double> coord = g.coord.to_host(), U = c->fs.U.to_host(), nu;
   const int nTurb = c->cfg.rans_sa ? 1 : 0;
+  SU2B_REQUIRE(!c->cfg.rans_sst, "restart files of SST runs are not supported");
   if (nTurb) nu = c->fs.nu.to_host();
   const int rc = su2b200_restart_write_arrays(path, binary, nd, nTurb, Pd, global_index, nPointGlobal ? nPointGlobal : Pd,
                                               coord.data(), U.data(), nTurb ? nu.data() : nullptr,
@@ -246,6 +247,7 @@ int su2b200_restart_read(su2b200_ctx* c, const char* path, const unsigned long* 
   const ulong_t P = (ulong_t)g.P;
   const int nd = g.nDim, nv = nd + 2;
   const int nTurb = c->cfg.rans_sa ? 1 : 0;
+  SU2B_REQUIRE(!c->cfg.rans_sst, "restart files of SST runs are not supported");
   std::vector<double> U((size_t)P * nv), nu(nTurb ? P : 0);
   const int rc = su2b200_restart_read_arrays(path, nd, nTurb, P, global_index, U.data(), nTurb ? nu.data() : nullptr);
   if (rc) throw Error(su2b200_last_error());

@@ -319,9 +319,16 @@ __global__ void k_turb_mut(int P, int neg, const double* __restrict__ V, const d
 }
 
 // ---- host wrappers ------------------------------------------------------------------------------------------------------
+// SST counterparts (turb_sst.cu)
+void sst_preprocessing(su2b200_ctx* c);
+void sst_space_integration(su2b200_ctx* c);
+void sst_complete_implicit(su2b200_ctx* c);
+void sst_postprocessing(su2b200_ctx* c);
+
 void turb_preprocessing(su2b200_ctx* c) {
   auto& s = c->fs;
-  SU2B_REQUIRE(c->cfg.rans_sa, "turbulence entry point called without KIND_TURB_MODEL= SA");
+  if (c->cfg.rans_sst) return sst_preprocessing(c);
+  SU2B_REQUIRE(c->cfg.rans_sa, "turbulence entry point called without KIND_TURB_MODEL= SA or SST");
   // residual and Jacobian are fully overwritten by the point kernel / edge kernel; halo rows are zeroed here
   scalar_gradient(c, c->cfg.grad_method, s.nu.p, s.nu_grad.p);
   if (c->nranks > 1) halo_exchange(c, s.nu_grad.p, c->geo.nDim);
@@ -335,6 +342,7 @@ void turb_set_time_step(su2b200_ctx* c) {
 }
 
 void turb_space_integration(su2b200_ctx* c) {
+  if (c->cfg.rans_sst) return sst_space_integration(c);
   ++c->sys[1].A_gen;
   auto& g = c->geo;
   auto& s = c->fs;
@@ -383,6 +391,7 @@ void turb_space_integration(su2b200_ctx* c) {
 }
 
 void turb_complete_implicit(su2b200_ctx* c) {
+  if (c->cfg.rans_sst) return sst_complete_implicit(c);
   ProfScope prof_(c, PROF_UPDATE);
   auto& g = c->geo;
   auto& s = c->fs;
@@ -392,6 +401,7 @@ void turb_complete_implicit(su2b200_ctx* c) {
 }
 
 void turb_postprocessing(su2b200_ctx* c) {
+  if (c->cfg.rans_sst) return sst_postprocessing(c);
   ProfScope prof_(c, PROF_TURB_OTHER);
   auto& g = c->geo;
   auto& s = c->fs;

@@ -91,7 +91,7 @@ class FlowSolver:
     def configure(self, **kw):
         cfg = default_config()
         for k, v in kw.items():
-            if k in ("velocity_inf", "ref_origin", "cfl_adapt_param"):
+            if k in ("velocity_inf", "ref_origin", "cfl_adapt_param", "sst_lower", "sst_upper"):
                 arr = getattr(cfg, k)
                 for i, x in enumerate(v):
                     arr[i] = float(x)
@@ -258,9 +258,9 @@ class FlowSolver:
         check(self.lib.su2b200_turb_space_integration(self.ctx))
 
     def Turb_PrepareImplicitIteration(self):
-        rms, mx, idx = C.c_double(), C.c_double(), C.c_ulong()
-        check(self.lib.su2b200_turb_prepare_implicit(self.ctx, C.byref(rms), C.byref(mx), C.byref(idx)))
-        return rms.value
+        rms, mx, idx = (C.c_double * 2)(), (C.c_double * 2)(), (C.c_ulong * 2)()  # one entry per turbulence variable
+        check(self.lib.su2b200_turb_prepare_implicit(self.ctx, rms, mx, idx))
+        return rms[0] if not self.cfg.rans_sst else (rms[0], rms[1])
 
     def Turb_Solve(self):
         it, res = C.c_ulong(0), C.c_double(0)
@@ -279,7 +279,7 @@ class FlowSolver:
         check(self.lib.su2b200_iterate(self.ctx, int(n), reps))
         out = []
         for r in reps:
-            out.append(dict(rms_flow=np.array(r.rms_flow[:self.nVar]), rms_turb=r.rms_turb, CL=r.CL, CD=r.CD,
+            out.append(dict(rms_flow=np.array(r.rms_flow[:self.nVar]), rms_turb=r.rms_turb, rms_turb2=r.rms_turb2, CL=r.CL, CD=r.CD,
                             linsol_iter_flow=r.linsol_iter_flow, linsol_res_flow=r.linsol_res_flow,
                             linsol_iter_turb=r.linsol_iter_turb, linsol_res_turb=r.linsol_res_turb,
                             nonphysical_points=r.nonphysical_points, nonphysical_edges=r.nonphysical_edges))
@@ -499,6 +499,8 @@ def default_config():
     c.assembly, c.prec_partitions = capi.ASSEMBLY_GATHER, 1
     c.turb_reducer, c.mg_level, c.lax_kappa1 = -1, 0, 0.15
     c.cfl_adapt, c.n_inner_iter = 0, 1000
+    c.rans_sst, c.max_update_sst = 0, 1.0   # MAX_UPDATE_SST
+    c.sst_lower[0], c.sst_lower[1], c.sst_upper[0], c.sst_upper[1] = 1.0e-10, 1.0e-4, 1.0e10, 1.0e15
     for k, v in enumerate((0.1, 1.2, 10.0, 100.0, 0.001, 0.0)):  # default_cfl_adapt (CConfig.cpp:1831-1836)
         c.cfl_adapt_param[k] = v
     return c

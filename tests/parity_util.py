@@ -70,7 +70,10 @@ def init_state_from_gold(s, gold, it):
     nd, P = s.nDim, s.nPoint
     s.set("SOLUTION", gold[pre + "pre_solution"])
     s.set("SOLUTION_OLD", gold[pre + "pre_solution_old"])
-    if s.cfg.rans_sa:
+    if s.cfg.rans_sst:
+        for name, key in (("SST_F1", "F1"), ("SST_F2", "F2"), ("SST_CDKW", "CDkw")):
+            s.set(name, gold[pre + "turb_pre_" + key])
+    if s.cfg.rans_sa or s.cfg.rans_sst:
         s.set("EDDY_VISC", gold[pre + "pre_primitive"].reshape(P, nd + 9)[:, nd + 6])
         s.set("TURB_SOLUTION", gold[pre + "turb_pre_solution"])
         s.set("TURB_SOLUTION_OLD", gold[pre + "turb_pre_solution"])
@@ -180,8 +183,9 @@ def run_turb_iteration(s, gold, it=0, report=None):
     s.Turb_Preprocessing()
 
 
-    g = gold[pre + "pre_gradient"].reshape(P, nd)[:s.nPointDomain]
-    e = relerr(s.get("TURB_GRADIENT").reshape(P, nd)[:s.nPointDomain], g)
+    nt = 2 if s.cfg.rans_sst else 1
+    g = gold[pre + "pre_gradient"].reshape(P, nt * nd)[:s.nPointDomain]
+    e = relerr(s.get("TURB_GRADIENT").reshape(P, nt * nd)[:s.nPointDomain], g)
     if report is not None:
         report["turb_gradient"] = e
     s.set("TURB_SOLUTION_OLD", s.get("TURB_SOLUTION"))  # Set_OldSolution
@@ -199,4 +203,8 @@ def run_turb_iteration(s, gold, it=0, report=None):
     s.Turb_Postprocessing()
     cmp("turb_post_solution", s.get("TURB_SOLUTION"), pre + "post_solution")
     cmp("turb_post_mut", s.get("EDDY_VISC"), pre + "post_mut")
+    if s.cfg.rans_sst:
+        cmp("sst_F1", s.get("SST_F1"), pre + "post_F1")
+        cmp("sst_F2", s.get("SST_F2"), pre + "post_F2")
+        cmp("sst_CDkw", s.get("SST_CDKW"), pre + "post_CDkw")
     return iters

@@ -15,7 +15,7 @@ from su2_b200.mesh import Mesh
 
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 CASES = ["naca0012_roe", "naca0012_jst", "box_euler", "rect_ns", "box_rans_sa", "rect_rans_sa", "naca0012_jacobi",
-         "naca0012_fgmres_lusgs", "naca0012_bcgstab_ilu", "naca0012_rfgmres", "naca0012_ls"]
+         "naca0012_fgmres_lusgs", "naca0012_bcgstab_ilu", "naca0012_rfgmres", "naca0012_ls", "box_rans_sst", "rect_rans_sst"]
 GENERATED = ["box_euler", "rect_ns", "box_rans_sa"]
 
 
@@ -64,7 +64,9 @@ def test_cfg_front_end_matches_reference_config(case):
     got = flow_config_from_cfg(opts, int(gold["nDim"]))
     skip = {"turb_linear_solver", "turb_linear_prec", "turb_linear_tol", "turb_linear_iter"}
     if not ref["rans_sa"]:
-        skip |= {"nu_tilde_inf", "eddy_visc_inf"}  # set by the reference whatever the solver, unused without SA
+        skip |= {"nu_tilde_inf"}  # set by the reference whatever the solver, unused without SA
+        if not ref.get("rans_sst"):
+            skip |= {"eddy_visc_inf"}  # set by the reference whatever the solver, unused without SA
     for k, v in ref.items():
         if k in skip or k not in got:
             continue

@@ -122,6 +122,53 @@ def test_rans_sa_history(case):
         assert r["linsol_iter_flow"] == int(hist[i, 8]) and r["linsol_iter_turb"] == int(hist[i, 10]), (i, r, hist[i])
 
 
+# ---- Menter SST: two turbulence variables, k in the flow's static energy ---------------------------------
+SST_CASES = ["box_rans_sst", "rect_rans_sst"]
+
+
+@pytest.mark.parametrize("case", SST_CASES)
+def test_rans_sst_stage_by_stage(case):
+    """Flow + SST iteration against the reference at every dumped iteration (3-D hex box, 2-D RECTANGLE): flow stages as
+    for SA (the primitives now take k out of the static energy), then gradient of (k, omega), convective + diffusive +
+    source residual and 2x2 Jacobian after the boundary conditions, Krylov solution, clipped conservative update, and
+    F1 / F2 / CDkw / muT of the post-processing."""
+    gold = _gold(case)
+    for it in _dump_iters(gold):
+        s = make_solver(gold)
+        report = {}
+        run_first_iteration(s, gold, it, report)
+        run_turb_iteration(s, gold, it, report)
+        s.close()
+        print(case, "it", it, {k: ("%.2e" % v if isinstance(v, float) else v) for k, v in report.items()})
+        tol = dict(TOL, turb_linsyssol=1e-7, turb_post_solution=1e-9, turb_post_mut=1e-8, sst_F1=1e-9, sst_F2=1e-9, sst_CDkw=1e-8)
+        noise = ("bc_residual", "rhs", "res_rms", "linsyssol", "post_solution") if it == 0 else ()
+        bad = {k: v for k, v in report.items()
+               if isinstance(v, float) and k.split("/")[0] not in noise and not (v <= _tol(tol, k))}
+        assert not bad, (it, bad)
+
+
+@pytest.mark.parametrize("case", SST_CASES)
+def test_rans_sst_history(case):
+    gold = _gold(case)
+    s = make_solver(gold)
+    n = int(gold["nIter"])
+    reps = s.iterate(n)
+    s.close()
+    hist = gold["history"]
+    nv = s.nVar
+    for i, r in enumerate(reps):
+        ref_rms = hist[i, :nv]
+        if np.max(np.abs(ref_rms)) >= 1e-14:  # iteration 0 of the flow is round-off in both codes
+            ok = np.abs(r["rms_flow"] - ref_rms) <= 1e-6 * np.abs(ref_rms) + 1e-12 * np.max(np.abs(ref_rms))
+            assert ok.all(), (i, r["rms_flow"], ref_rms)
+        assert abs(r["rms_turb"] - hist[i, 5]) <= 1e-6 * abs(hist[i, 5]), (i, r["rms_turb"], hist[i, 5])
+        assert abs(r["rms_turb2"] - hist[i, 12]) <= 1e-6 * abs(hist[i, 12]), (i, r["rms_turb2"], hist[i, 12])
+        assert abs(r["CD"] - hist[i, 7]) <= 1e-6 * max(1e-3, abs(hist[i, 7])), (i, r["CD"], hist[i, 7])
+        assert r["linsol_iter_turb"] == int(hist[i, 10]), (i, r, hist[i])
+        if np.max(np.abs(ref_rms)) >= 1e-14:  # a right-hand side of pure round-off: the Krylov count means nothing
+            assert r["linsol_iter_flow"] == int(hist[i, 8]), (i, r, hist[i])
+
+
 # ---- code paths that round 1 shipped untested ------------------------------------------------------------------------
 @pytest.mark.parametrize("case", VARIANTS)
 def test_linear_solver_and_gradient_variants(case):

@@ -4,7 +4,7 @@ set -e
 name=$1; shift
 cd "$(dirname "$0")/../su2_b200/csrc"
 out=../variants; mkdir -p $out/obj_$name
-for f in capi.cu capi_flow.cu flow_kernels.cu edge_kernels.cu bc_kernels.cu linalg.cu precond.cu precond_poll.cu precond_factor.cu krylov.cu comm.cu turb_sa.cu mesh_host.cu restart_host.cu; do
+for f in capi.cu capi_flow.cu flow_kernels.cu edge_kernels.cu bc_kernels.cu linalg.cu precond.cu precond_poll.cu precond_factor.cu krylov.cu comm.cu turb_sa.cu turb_sst.cu mesh_host.cu restart_host.cu; do
   ( /usr/local/cuda/bin/nvcc -gencode arch=compute_100a,code=sm_100a -O3 -std=c++17 -lineinfo -Xcompiler -fPIC --expt-relaxed-constexpr "$@" -c $f -o $out/obj_$name/${f%.cu}.o ) &
 done
 wait
