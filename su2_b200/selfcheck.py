@@ -28,8 +28,9 @@ def _perturb(s, xyz, rans):
     for name in ("SOLUTION", "SOLUTION_OLD"):
         s.set(name, (s.get(name).reshape(-1, nv) * bump[:, None]).ravel())
     if rans:
-        for name in ("TURB_SOLUTION", "TURB_SOLUTION_OLD"):
-            s.set(name, s.get(name) * bump)
+        for name in ("TURB_SOLUTION", "TURB_SOLUTION_OLD"):  # [P] (SA) or [P][2] (SST)
+            t = s.get(name)
+            s.set(name, (t.reshape(len(bump), -1) * bump[:, None]).ravel())
 
 
 def unstructured_mesh(opts, path, rank, world, nparts):
@@ -87,7 +88,7 @@ def run_iterations(cfg_text, n_iter, rank, world, device, comm_id=None, partitio
         s.configure(**kw)
         s.allocate()
         mesh.close()
-        rans = bool(kw["rans_sa"])
+        rans = bool(kw["rans_sa"]) or bool(kw.get("rans_sst"))
         if partition_planes is not None:
             plane = Pd // partition_planes[-1]
             part_rows = [p * plane for p in partition_planes]
@@ -105,7 +106,7 @@ def run_iterations(cfg_text, n_iter, rank, world, device, comm_id=None, partitio
             iters=np.array([r["linsol_iter_flow"] for r in reps]),
             CL=np.array([r["CL"] for r in reps]), CD=np.array([r["CD"] for r in reps]))
         if rans:
-            out["nu"] = s.get("TURB_SOLUTION")[:Pd].copy()
+            out["nu"] = s.get("TURB_SOLUTION").reshape(P, -1)[:Pd].copy()
             out["rms_turb"] = np.array([r["rms_turb"] for r in reps])
             out["iters_turb"] = np.array([r["linsol_iter_turb"] for r in reps])
         return gid[:Pd], out

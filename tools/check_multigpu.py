@@ -82,7 +82,10 @@ def whole_iterations(kind, rank, world, local):
             m.write_su2(su2_path)
             m.close()
         dist.barrier()
-    text = bench.make_cfg(kind, [12, 10, n_planes], 1)
+    sst = kind == "SST"
+    text = bench.make_cfg("RANS" if sst else kind, [12, 10, n_planes], 1)
+    if sst:
+        text = text.replace("KIND_TURB_MODEL= SA", "KIND_TURB_MODEL= SST")
     if su2_path:
         text = text.replace("MESH_FORMAT= BOX", "MESH_FORMAT= SU2\nMESH_FILENAME= " + su2_path)
 
