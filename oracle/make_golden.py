@@ -43,6 +43,7 @@ CASES = {
     # Menter SST (V2003m): two-variable turbulence system, k in the flow's static energy
     "box_rans_sst": ("box_rans_sst.cfg", 6, "0,1,2", 2, None),
     "rect_rans_sst": ("rect_rans_sst.cfg", 6, "0,1,2", 2, None),
+    "rect_rans_sst_wls": ("rect_rans_sst_wls.cfg", 6, "0,1", None, None),  # weighted least squares for the (k, omega) gradient too
     # FAS multigrid: C1 as shipped (3 coarse levels, W-cycle); agglomerated levels + every transfer step of iteration 0
     "naca0012_mg": ("naca0012_mg.cfg", 30, "0", None, "mesh_NACA0012_inv.su2"),
 }

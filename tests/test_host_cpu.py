@@ -15,7 +15,7 @@ from su2_b200.mesh import Mesh
 
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 CASES = ["naca0012_roe", "naca0012_jst", "box_euler", "rect_ns", "box_rans_sa", "rect_rans_sa", "naca0012_jacobi",
-         "naca0012_fgmres_lusgs", "naca0012_bcgstab_ilu", "naca0012_rfgmres", "naca0012_ls", "box_rans_sst", "rect_rans_sst"]
+         "naca0012_fgmres_lusgs", "naca0012_bcgstab_ilu", "naca0012_rfgmres", "naca0012_ls", "box_rans_sst", "rect_rans_sst", "rect_rans_sst_wls"]
 GENERATED = ["box_euler", "rect_ns", "box_rans_sa"]
 
 

@@ -123,7 +123,7 @@ def test_rans_sa_history(case):
 
 
 # ---- Menter SST: two turbulence variables, k in the flow's static energy ---------------------------------
-SST_CASES = ["box_rans_sst", "rect_rans_sst"]
+SST_CASES = ["box_rans_sst", "rect_rans_sst", "rect_rans_sst_wls"]
 
 
 @pytest.mark.parametrize("case", SST_CASES)
