@@ -57,45 +57,56 @@ static NcclApi& nccl() {
     if (r_ != 0) throw Error(std::string(#call) + " failed: " + nccl().GetErrorString(r_));     \
   } while (0)
 
-__global__ void k_pack(int n, int cnt, const int* __restrict__ idx, const double* __restrict__ arr,
-                       double* __restrict__ buf) {
+template <class T>
+__global__ void k_pack(int n, int cnt, const int* __restrict__ idx, const T* __restrict__ arr, T* __restrict__ buf) {
   const int t = blockIdx.x * blockDim.x + threadIdx.x;
   if (t >= n * cnt) return;
   const int p = t / cnt, k = t % cnt;
   buf[t] = arr[(size_t)idx[p] * cnt + k];
 }
-__global__ void k_unpack(int n, int cnt, const int* __restrict__ idx, const double* __restrict__ buf,
-                         double* __restrict__ arr) {
+template <class T>
+__global__ void k_unpack(int n, int cnt, const int* __restrict__ idx, const T* __restrict__ buf, T* __restrict__ arr) {
   const int t = blockIdx.x * blockDim.x + threadIdx.x;
   if (t >= n * cnt) return;
   const int p = t / cnt, k = t % cnt;
   arr[(size_t)idx[p] * cnt + k] = buf[t];
 }
 
-void halo_exchange(su2b200_ctx* c, double* arr, int cnt) {
+// ncclDataType_t: ncclFloat32 = 7, ncclFloat64 = 8; the staging buffers are sized in doubles and reused for floats
+template <class T> struct NcclType;
+template <> struct NcclType<double> { static constexpr int id = 8; };
+template <> struct NcclType<float> { static constexpr int id = 7; };
+
+template <class T>
+static void halo_exchange_impl(su2b200_ctx* c, T* arr, int cnt) {
   if (c->nranks <= 1 || c->p2p_ranks.empty()) return;
   SU2B_REQUIRE(c->nccl, "halo exchange requested without a communicator (su2b200_comm_init)");
   const int nn = (int)c->p2p_ranks.size();
   const int nsend = c->p2p_send_ptr[nn], nrecv = c->p2p_recv_ptr[nn];
   if (c->p2p_send_buf.n < (size_t)nsend * cnt) c->p2p_send_buf.alloc((size_t)nsend * cnt);
   if (c->p2p_recv_buf.n < (size_t)nrecv * cnt) c->p2p_recv_buf.alloc((size_t)nrecv * cnt);
-  SU2B_LAUNCH(c, k_pack, nblk((long)nsend * cnt, 256), 256, nsend, cnt, c->p2p_send_idx.p, arr, c->p2p_send_buf.p);
+  T* sendb = reinterpret_cast<T*>(c->p2p_send_buf.p);
+  T* recvb = reinterpret_cast<T*>(c->p2p_recv_buf.p);
+  SU2B_LAUNCH(c, k_pack<T>, nblk((long)nsend * cnt, 256), 256, nsend, cnt, c->p2p_send_idx.p, arr, sendb);
   auto& api = nccl();
   SU2B_NCCL(api.GroupStart());
   for (int k = 0; k < nn; ++k) {
     const int ns = c->p2p_send_ptr[k + 1] - c->p2p_send_ptr[k], nr = c->p2p_recv_ptr[k + 1] - c->p2p_recv_ptr[k];
-    if (nr) SU2B_NCCL(api.Recv(c->p2p_recv_buf.p + (size_t)c->p2p_recv_ptr[k] * cnt, (size_t)nr * cnt, 8, c->p2p_ranks[k], c->nccl, c->stream));
-    if (ns) SU2B_NCCL(api.Send(c->p2p_send_buf.p + (size_t)c->p2p_send_ptr[k] * cnt, (size_t)ns * cnt, 8, c->p2p_ranks[k], c->nccl, c->stream));
+    if (nr) SU2B_NCCL(api.Recv(recvb + (size_t)c->p2p_recv_ptr[k] * cnt, (size_t)nr * cnt, NcclType<T>::id, c->p2p_ranks[k], c->nccl, c->stream));
+    if (ns) SU2B_NCCL(api.Send(sendb + (size_t)c->p2p_send_ptr[k] * cnt, (size_t)ns * cnt, NcclType<T>::id, c->p2p_ranks[k], c->nccl, c->stream));
   }
   SU2B_NCCL(api.GroupEnd());
-  SU2B_LAUNCH(c, k_unpack, nblk((long)nrecv * cnt, 256), 256, nrecv, cnt, c->p2p_recv_idx.p, c->p2p_recv_buf.p, arr);
+  SU2B_LAUNCH(c, k_unpack<T>, nblk((long)nrecv * cnt, 256), 256, nrecv, cnt, c->p2p_recv_idx.p, recvb, arr);
 }
+void halo_exchange(su2b200_ctx* c, double* arr, int cnt) { halo_exchange_impl<double>(c, arr, cnt); }
+void halo_exchange(su2b200_ctx* c, float* arr, int cnt) { halo_exchange_impl<float>(c, arr, cnt); }
 
 // e3. The same exchange split in two so that interior work overlaps it: the pack runs on the compute stream (it reads what
 // the preceding kernel wrote), send/recv and the unpack run on comm_stream, and halo_exchange_finish makes the compute
 // stream wait for the unpack.  Between start and finish the compute stream may read the owned entries of `arr` and must
 // not trust (nor write) its halo entries.  One exchange in flight at a time (the staging buffers are shared).
-void halo_exchange_start(su2b200_ctx* c, double* arr, int cnt) {
+template <class T>
+static void halo_exchange_start_impl(su2b200_ctx* c, T* arr, int cnt) {
   if (c->nranks <= 1 || c->p2p_ranks.empty()) return;
   SU2B_REQUIRE(c->nccl, "halo exchange requested without a communicator (su2b200_comm_init)");
   SU2B_REQUIRE(!c->exchange_in_flight, "halo_exchange_start: the previous exchange was not finished");
@@ -108,23 +119,27 @@ void halo_exchange_start(su2b200_ctx* c, double* arr, int cnt) {
   const int nsend = c->p2p_send_ptr[nn], nrecv = c->p2p_recv_ptr[nn];
   if (c->p2p_send_buf.n < (size_t)nsend * cnt) c->p2p_send_buf.alloc((size_t)nsend * cnt);
   if (c->p2p_recv_buf.n < (size_t)nrecv * cnt) c->p2p_recv_buf.alloc((size_t)nrecv * cnt);
-  SU2B_LAUNCH(c, k_pack, nblk((long)nsend * cnt, 256), 256, nsend, cnt, c->p2p_send_idx.p, arr, c->p2p_send_buf.p);
+  T* sendb = reinterpret_cast<T*>(c->p2p_send_buf.p);
+  T* recvb = reinterpret_cast<T*>(c->p2p_recv_buf.p);
+  SU2B_LAUNCH(c, k_pack<T>, nblk((long)nsend * cnt, 256), 256, nsend, cnt, c->p2p_send_idx.p, arr, sendb);
   SU2B_CUDA(cudaEventRecord(c->ev_packed, c->stream));
   SU2B_CUDA(cudaStreamWaitEvent(c->comm_stream, c->ev_packed, 0));
   auto& api = nccl();
   SU2B_NCCL(api.GroupStart());
   for (int k = 0; k < nn; ++k) {
     const int ns = c->p2p_send_ptr[k + 1] - c->p2p_send_ptr[k], nr = c->p2p_recv_ptr[k + 1] - c->p2p_recv_ptr[k];
-    if (nr) SU2B_NCCL(api.Recv(c->p2p_recv_buf.p + (size_t)c->p2p_recv_ptr[k] * cnt, (size_t)nr * cnt, 8, c->p2p_ranks[k], c->nccl, c->comm_stream));
-    if (ns) SU2B_NCCL(api.Send(c->p2p_send_buf.p + (size_t)c->p2p_send_ptr[k] * cnt, (size_t)ns * cnt, 8, c->p2p_ranks[k], c->nccl, c->comm_stream));
+    if (nr) SU2B_NCCL(api.Recv(recvb + (size_t)c->p2p_recv_ptr[k] * cnt, (size_t)nr * cnt, NcclType<T>::id, c->p2p_ranks[k], c->nccl, c->comm_stream));
+    if (ns) SU2B_NCCL(api.Send(sendb + (size_t)c->p2p_send_ptr[k] * cnt, (size_t)ns * cnt, NcclType<T>::id, c->p2p_ranks[k], c->nccl, c->comm_stream));
   }
   SU2B_NCCL(api.GroupEnd());
-  k_unpack<<<nblk((long)nrecv * cnt, 256), 256, 0, c->comm_stream>>>(nrecv, cnt, c->p2p_recv_idx.p, c->p2p_recv_buf.p, arr);
+  k_unpack<T><<<nblk((long)nrecv * cnt, 256), 256, 0, c->comm_stream>>>(nrecv, cnt, c->p2p_recv_idx.p, recvb, arr);
   SU2B_CUDA(cudaGetLastError());
   ++c->launches;
   SU2B_CUDA(cudaEventRecord(c->ev_unpacked, c->comm_stream));
   c->exchange_in_flight = true;
 }
+void halo_exchange_start(su2b200_ctx* c, double* arr, int cnt) { halo_exchange_start_impl<double>(c, arr, cnt); }
+void halo_exchange_start(su2b200_ctx* c, float* arr, int cnt) { halo_exchange_start_impl<float>(c, arr, cnt); }
 void halo_exchange_finish(su2b200_ctx* c) {
   if (!c->exchange_in_flight) return;
   SU2B_CUDA(cudaStreamWaitEvent(c->stream, c->ev_unpacked, 0));
@@ -163,6 +178,11 @@ void allreduce_dev_sum(su2b200_ctx* c, double* d, int n) {
   if (c->nranks <= 1) return;
   SU2B_REQUIRE(c->nccl, "allreduce requested without a communicator");
   SU2B_NCCL(nccl().AllReduce(d, d, (size_t)n, 8, 0, c->nccl, c->stream));
+}
+void allreduce_dev_sum(su2b200_ctx* c, float* d, int n) {
+  if (c->nranks <= 1) return;
+  SU2B_REQUIRE(c->nccl, "allreduce requested without a communicator");
+  SU2B_NCCL(nccl().AllReduce(d, d, (size_t)n, 7, 0, c->nccl, c->stream));
 }
 
 // in-place allreduce of n (<= 32) host doubles; op: 0 sum, 2 max, 3 min (ncclRedOp_t)

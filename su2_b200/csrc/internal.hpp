@@ -118,7 +118,8 @@ struct Geometry {
 };
 
 // ---- block-CSR linear system (CSysMatrix + CSysVector + CSysSolve workspace) -----------------
-struct LinSys {
+template <class T>
+struct LinSysT {
   int nVar = 0;
   int P = 0, Pd = 0;
   long nnz = 0;
@@ -127,9 +128,9 @@ struct LinSys {
   const int* dia_ptr = nullptr;
   dvec<int> own_row_ptr, own_col_ind, own_dia_ptr;
   std::vector<int> h_row_ptr, h_col_ind, h_dia_ptr;
-  dvec<double> A;      // [nnz][nVar*nVar]
-  dvec<double> ilu;    // ILU_matrix
-  dvec<double> invM;   // [Pd][nVar*nVar] inverse diagonal (Jacobi or ILU's U_ii^-1)
+  dvec<T> A;      // [nnz][nVar*nVar]
+  dvec<T> ilu;    // ILU_matrix
+  dvec<T> invM;   // [Pd][nVar*nVar] inverse diagonal (Jacobi or ILU's U_ii^-1)
   // level schedule for exact ILU0 build/apply (rows grouped by dependency level)
   bool levels_ready = false;
   std::vector<int> lvl_ptr_lower, lvl_ptr_upper;  // host offsets into the row lists
@@ -165,31 +166,48 @@ struct LinSys {
   dvec<int> sweep_meta_lower, sweep_meta_upper;  // int4 {row, first, last+1, 0} per level-ordered position (mode 2)
   int poll_split_lower[4] = {0, 0, 0, 0}, poll_split_upper[4] = {0, 0, 0, 0};  // hybrid sweep: see build_meta
   int poll_groups_lower = 0, poll_groups_upper = 0;  // scalar systems: groups of 4 level-padded rows
-  dvec<double> sweep_tmp, sweep_tmp2;  // forward-sweep result / copy of an in-place rhs (mode 2)
+  dvec<T> sweep_tmp, sweep_tmp2;  // forward-sweep result / copy of an in-place rhs (mode 2)
   // reference-style row partitions (block-Jacobi ILU across partitions); nparts <= 1: exact serial factor
   int nparts = 1;
   std::vector<int> h_parts;
   dvec<int> parts;
   // Krylov workspace
-  std::vector<dvec<double>*> work;   // lazily grown pool of [P*nVar] vectors
-  dvec<double> scalars;              // device scalars for reductions
-  double* h_scalars = nullptr;       // pinned host mirror
-  double* h_mgs = nullptr;           // pinned: Hessenberg column of the device Gram-Schmidt
+  std::vector<dvec<T>*> work;   // lazily grown pool of [P*nVar] vectors
+  dvec<T> scalars;              // device scalars for reductions
+  T* h_scalars = nullptr;       // pinned host mirror
+  T* h_mgs = nullptr;           // pinned: Hessenberg column of the device Gram-Schmidt
   // fused upper product: a backward ILU sweep whose upper factor is the Jacobian's upper triangle (upper_stable) computes
   // sum_{j>i} A_ij z_j on its way; the product A z that follows in a Krylov iteration then only reads the lower triangle,
   // the diagonal and the halo columns (4 of 7 blocks on a hexahedral mesh) and adds it
-  dvec<double> upper_prod;               // [Pd][nVar]
-  const double* upper_prod_of = nullptr; // the vector z it belongs to (set by the apply, cleared by the next apply)
+  dvec<T> upper_prod;               // [Pd][nVar]
+  const T* upper_prod_of = nullptr; // the vector z it belongs to (set by the apply, cleared by the next apply)
   bool want_upper_prod = false;          // set by the Krylov solver around apply + product
   dvec<int> rest_halo_ptr;               // per owned row: first entry with a halo column (multi-rank only)
   bool rest_halo_ready = false;
   // owned rows with at least one halo column (multi-rank): redone by the overlapped product once the halos arrived
   dvec<int> halo_rows;
   int n_halo_rows = -1;              // -1: not built yet
-  ~LinSys();
-  dvec<double>& vec(size_t i);
+  ~LinSysT();
+  dvec<T>& vec(size_t i);
   size_t vecLen() const { return (size_t)P * nVar; }
 };
+template <class T>
+LinSysT<T>::~LinSysT() {
+  for (auto* v : work) delete v;
+  if (h_scalars) cudaFreeHost(h_scalars);
+  if (h_mgs) cudaFreeHost(h_mgs);
+}
+template <class T>
+dvec<T>& LinSysT<T>::vec(size_t i) {
+  while (work.size() <= i) work.push_back(new dvec<T>());
+  if (work[i]->n != vecLen()) {
+    work[i]->alloc(vecLen());
+    work[i]->zero();
+  }
+  return *work[i];
+}
+using LinSys = LinSysT<double>;
+using LinSysF = LinSysT<float>;  // the reference's mixed-precision mode (code_config.hpp:133-139)
 
 // ---- flow state ---------------------------------------------------------------------------------
 struct FlowState {
@@ -252,6 +270,7 @@ struct su2b200_ctx {
   bool configured = false;
   su2b200::FlowState fs;
   su2b200::LinSys sys[2];
+  su2b200::LinSysF sysf[2];  // single-precision copies for the mixed-precision linear solve (empty unless cfg.mixed_precision)
   // comm
   void* nccl = nullptr;
   int rank = 0, nranks = 1;

@@ -27,32 +27,26 @@ void flow_bc_sym_plane(su2b200_ctx* c, int iMarker);
 void flow_bc_heatflux_wall(su2b200_ctx* c, int iMarker);
 void flow_forces(su2b200_ctx* c, double* coeffs);
 
-// linalg.cu  (CSysMatrix / CSysVector)
-void linsys_bind_geometry(su2b200_ctx* c, int which, int nVar);
-void linsys_spmv(su2b200_ctx* c, LinSys& ls, const double* x, double* y);
-void linsys_spmv_exchange_x(su2b200_ctx* c, LinSys& ls, double* x, double* y);  // x: owned entries valid, halos exchanged here
-void linsys_build_jacobi(su2b200_ctx* c, LinSys& ls);
-void linsys_apply_jacobi(su2b200_ctx* c, LinSys& ls, const double* x, double* y);
-void linsys_build_ilu(su2b200_ctx* c, LinSys& ls);
-void linsys_apply_ilu(su2b200_ctx* c, LinSys& ls, const double* x, double* y);
-void linsys_apply_lusgs(su2b200_ctx* c, LinSys& ls, const double* x, double* y);
-void linsys_build_prec(su2b200_ctx* c, LinSys& ls, int prec);
-void linsys_apply_prec(su2b200_ctx* c, LinSys& ls, int prec, const double* x, double* y);
-void linsys_prec_then_product(su2b200_ctx* c, LinSys& ls, int prec, const double* v, double* z, double* w);  // z = M^-1 v, w = A z
-void linsys_check_sweeps(su2b200_ctx* c, LinSys& ls);  // throws if the sweep watchdog fired
-void ilu_apply_poll(su2b200_ctx* c, LinSys& ls, const double* x, double* y);  // precond_poll.cu
-bool factor_symbolic(LinSys& ls);                                             // precond_factor.cu
-void ilu_factor_poll(su2b200_ctx* c, LinSys& ls);
-double vec_dot(su2b200_ctx* c, LinSys& ls, const double* a, const double* b);
-void vec_axpy(su2b200_ctx* c, size_t n, double alpha, const double* x, double* y);           // y += alpha x
-void vec_axpby(su2b200_ctx* c, size_t n, double alpha, const double* x, double beta, double* y);  // y = alpha x + beta y
-void vec_scale(su2b200_ctx* c, size_t n, double alpha, double* x);
-void vec_copy(su2b200_ctx* c, size_t n, const double* x, double* y);
-void vec_set_scaled(su2b200_ctx* c, size_t n, double alpha, const double* x, double* y);     // y = alpha x
-
-// krylov.cu  (CSysSolve)
-unsigned long linsys_solve(su2b200_ctx* c, LinSys& ls, int solver, int prec, double tol, int max_iter,
-                           int restart, const double* b, double* x, double* residual);
+// linalg.cu, precond.cu, precond_poll.cu, precond_factor.cu, krylov.cu are compiled twice: namespace f64 (real = double, the path
+// every parity gate runs) and namespace f32 (real = float: the reference's mixed-precision mode, su2mixedfloat = float,
+// code_config.hpp:133-139, where the Jacobian, the preconditioner and every Krylov vector are single precision).  Both sets
+// of overloads are visible in su2b200; the LinSysT<double> / LinSysT<float> argument selects.
+#define real double
+#define LinSysR LinSysT<double>
+namespace f64 {
+#include "linalg_decl.inc"
+}
+#undef real
+#undef LinSysR
+#define real float
+#define LinSysR LinSysT<float>
+namespace f32 {
+#include "linalg_decl.inc"
+}
+#undef real
+#undef LinSysR
+using namespace f64;
+using namespace f32;
 
 // turb_sa.cu
 void turb_preprocessing(su2b200_ctx* c);
@@ -63,10 +57,13 @@ void turb_postprocessing(su2b200_ctx* c);
 
 // comm.cu
 void halo_exchange(su2b200_ctx* c, double* arr, int count_per_point);
+void halo_exchange(su2b200_ctx* c, float* arr, int count_per_point);
+void halo_exchange_start(su2b200_ctx* c, float* arr, int count_per_point);
 void halo_exchange_start(su2b200_ctx* c, double* arr, int count_per_point);  // returns at once; the halos of arr are in flight
 void halo_exchange_finish(su2b200_ctx* c);                                   // the compute stream waits for them
 double allreduce_sum(su2b200_ctx* c, double v);
 void allreduce_dev_sum(su2b200_ctx* c, double* d, int n);       // device buffer, in stream
+void allreduce_dev_sum(su2b200_ctx* c, float* d, int n);
 // Mailbox allreduce of ONE double inside a kernel (one block; every thread of it must call): see comm.cu
 struct MailboxView {
   unsigned long long* local;
