@@ -261,6 +261,10 @@ typedef struct {
   double kine_inf, omega_inf;        /* Solution_Inf: 3/2 |v_inf|^2 I^2 and rho_inf k_inf / (mu_inf ratio)             */
   double sst_lower[2], sst_upper[2]; /* lowerlimit / upperlimit of (k, omega): 1e-10, 1e-4 / 1e10, 1e15 without DLL    */
   double max_update_sst;             /* MAX_UPDATE_SST (1.0)                                                           */
+  /* The reference's mixed-precision build (meson -Denable-mixedprec=true: su2mixedfloat = float, code_config.hpp:133-139;
+   * CSysSolve::HandleTemporariesIn/Out, CSysSolve.hpp:242-286): Jacobian, preconditioner and all Krylov vectors of the
+   * flow and turbulence solves in single precision, residual assembly and update in double. */
+  int mixed_precision;
 } su2b200_flow_config;
 
 int su2b200_flow_configure(su2b200_ctx* ctx, const su2b200_flow_config* cfg);

@@ -66,6 +66,9 @@ HISTORIES = {
     "naca0012_jst_long": ("naca0012_jst", {}, 600, 1),
     "box_rans_sa_long": ("box_rans_sa", {}, 250, 1),
     "box_rans_sa_t4": ("box_rans_sa", {"MESH_BOX_SIZE": "21,17,13", "LINEAR_SOLVER_ITER": "25"}, 12, 4),
+    # the reference built with -Denable-mixedprec=true (oracle/build_ref_mixed.sh): single-precision Jacobian and Krylov solve
+    "box_rans_sa_mixed": ("box_rans_sa", {"MESH_BOX_SIZE": "21,17,13"}, 20, 1, "SU2_CFD_mixed"),
+    "naca0012_roe_mixed": ("naca0012_roe", {}, 40, 1, "SU2_CFD_mixed"),
 }
 MATRIX_KEYS = ("_jacobian", "_ilu", "_invM")
 KEEP_MATRICES = ("bc_jacobian", "_ilu", "_invM", "turb_bc_jacobian", "turb_src_jacobian", "turb_edge_jacobian", "turb_conv_jacobian")
@@ -177,9 +180,10 @@ def _history_from_csv(path):
 
 
 def run_history(name, out_dir=None):
-    base, over, nit, threads = HISTORIES[name]
+    base, over, nit, threads, *rest = HISTORIES[name]
+    exe = rest[0] if rest else "SU2_CFD"
     text = cfg_with(_case_text(base), dict(over, ITER=str(nit)))
-    if threads == 1:
+    if threads == 1 and exe == "SU2_CFD":
         d = _dump(text, "case.cfg", CASES[base][4], nit, "")
         slim = {k: v for k, v in d.items() if k.startswith(("cfg_", "enum_", "nDim", "nPoint", "nEdge", "nMarker"))
                 or k in ("history", "nIter")}
@@ -196,7 +200,7 @@ def run_history(name, out_dir=None):
     try:
         _stage(tmp, text, "case.cfg", CASES[base][4])
         env = dict(os.environ, OMP_NUM_THREADS=str(threads))
-        subprocess.run([os.path.join(HERE, "_ref", "SU2_CFD"), "-t", str(threads), "case.cfg"], cwd=tmp, env=env, check=True,
+        subprocess.run([os.path.join(HERE, "_ref", exe), "-t", str(threads), "case.cfg"], cwd=tmp, env=env, check=True,
                        stdout=subprocess.DEVNULL)
         hist = _history_from_csv(os.path.join(tmp, "history.csv"))
     finally:
@@ -206,6 +210,7 @@ def run_history(name, out_dir=None):
     slim["history"] = hist
     slim["nIter"] = len(hist)
     slim["threads"] = threads
+    slim["mixed_precision"] = int(exe == "SU2_CFD_mixed")
     return _save(name, slim, out_dir)
 
 

@@ -58,6 +58,7 @@ class FlowConfig(C.Structure):
         ("mg_level", C.c_int), ("lax_kappa1", C.c_double),
         ("rans_sst", C.c_int), ("kine_inf", C.c_double), ("omega_inf", C.c_double),
         ("sst_lower", C.c_double * 2), ("sst_upper", C.c_double * 2), ("max_update_sst", C.c_double),
+        ("mixed_precision", C.c_int),
     ]
 
 

@@ -101,13 +101,64 @@ static void flow_space_integration(su2b200_ctx* c, unsigned long* nonphys_edges)
     if (mk[m].kind == SU2B200_SYMMETRY_PLANE || mk[m].kind == SU2B200_EULER_WALL) flow_bc_sym_plane(c, (int)m);
 }
 
+// f2. The reference's mixed-precision mode (-Denable-mixedprec: su2mixedfloat = float, code_config.hpp:133-139): the
+// Jacobian, the preconditioner and every Krylov vector are single precision; CSysSolve::HandleTemporariesIn/Out
+// (CSysSolve.hpp:242-286) copy LinSysRes / LinSysSol to and from float vectors around the solve.  Here the Jacobian is
+// assembled in double as always, rounded once into the float system (the reference rounds every contribution as it adds
+// it), and the whole solve runs on the f32 instantiation of the linear algebra (linalg/precond*/krylov *_impl.inc).
+template <class Tin, class Tout>
+__global__ void k_convert(size_t n, const Tin* __restrict__ a, Tout* __restrict__ b) {
+  for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (size_t)gridDim.x * blockDim.x) b[i] = (Tout)a[i];
+}
+static unsigned long mixed_solve(su2b200_ctx* c, int which, int solver, int prec, double tol, int max_iter, int restart,
+                                 const double* b, double* x, double* residual) {
+  LinSys& ls = c->sys[which];
+  LinSysF& lf = c->sysf[which];
+  if (lf.nVar != ls.nVar || lf.nnz != ls.nnz || lf.P != ls.P) {  // bind to the same pattern
+    lf.nVar = ls.nVar; lf.P = ls.P; lf.Pd = ls.Pd; lf.nnz = ls.nnz;
+    lf.row_ptr = ls.row_ptr; lf.col_ind = ls.col_ind; lf.dia_ptr = ls.dia_ptr;
+    lf.h_row_ptr = ls.h_row_ptr; lf.h_col_ind = ls.h_col_ind; lf.h_dia_ptr = ls.h_dia_ptr;
+    lf.levels_ready = false;
+    lf.A.alloc((size_t)ls.nnz * ls.nVar * ls.nVar);
+  }
+  lf.nparts = ls.nparts; lf.h_parts = ls.h_parts; lf.parts_explicit = ls.parts_explicit;
+  lf.sweep_mode = ls.sweep_mode; lf.build_mode = ls.build_mode;
+  lf.wide_sweep = ls.wide_sweep; lf.wide_factor = ls.wide_factor; lf.factor_rows_mode = ls.factor_rows_mode;
+  const size_t nA = lf.A.n, nV = ls.vecLen();
+  const int grid = 148 * 8;
+  SU2B_LAUNCH(c, (k_convert<double, float>), grid, 256, nA, (const double*)ls.A.p, lf.A.p);
+  ++lf.A_gen;
+  const int top = 2 * (std::max(max_iter, 6) + 1) + 2;  // above the solver's own workspace
+  float* fb = lf.vec(top).p;
+  float* fx = lf.vec(top + 1).p;
+  SU2B_LAUNCH(c, (k_convert<double, float>), grid, 256, nV, b, fb);
+  SU2B_CUDA(cudaMemsetAsync(fx, 0, nV * sizeof(float), c->stream));
+  float res = 0.0f;
+  const unsigned long it = linsys_solve(c, lf, solver, prec, (float)tol, max_iter, restart, (const float*)fb, fx, &res);
+  SU2B_LAUNCH(c, (k_convert<float, double>), grid, 256, nV, (const float*)fx, x);
+  if (residual) *residual = (double)res;
+  return it;
+}
+
 static void flow_linear_solve(su2b200_ctx* c) {
   auto& s = c->fs;
   const auto& cfg = c->cfg;
   double res = 0.0;
-  c->lin_iters[0] = linsys_solve(c, c->sys[0], cfg.linear_solver, cfg.linear_prec, cfg.linear_tol, cfg.linear_iter,
-                                 cfg.linear_restart, s.res.p, s.sol.p, &res);
+  if (cfg.mixed_precision)
+    c->lin_iters[0] = mixed_solve(c, 0, cfg.linear_solver, cfg.linear_prec, cfg.linear_tol, cfg.linear_iter,
+                                  cfg.linear_restart, s.res.p, s.sol.p, &res);
+  else
+    c->lin_iters[0] = linsys_solve(c, c->sys[0], cfg.linear_solver, cfg.linear_prec, cfg.linear_tol, cfg.linear_iter,
+                                   cfg.linear_restart, s.res.p, s.sol.p, &res);
   c->lin_res[0] = res;
+}
+static unsigned long turb_linear_solve(su2b200_ctx* c, double* res) {
+  const auto& cfg = c->cfg;
+  if (cfg.mixed_precision)
+    return mixed_solve(c, 1, cfg.turb_linear_solver, cfg.turb_linear_prec, cfg.turb_linear_tol, cfg.turb_linear_iter,
+                       cfg.linear_restart, c->fs.turb_res.p, c->fs.turb_sol.p, res);
+  return linsys_solve(c, c->sys[1], cfg.turb_linear_solver, cfg.turb_linear_prec, cfg.turb_linear_tol, cfg.turb_linear_iter,
+                      cfg.linear_restart, c->fs.turb_res.p, c->fs.turb_sol.p, res);
 }
 
 extern "C" {
@@ -235,8 +286,7 @@ int su2b200_turb_linear_solve(su2b200_ctx* c, unsigned long* iterations, double*
   require_flow(c);
   const auto& cfg = c->cfg;
   double res = 0.0;
-  c->lin_iters[1] = linsys_solve(c, c->sys[1], cfg.turb_linear_solver, cfg.turb_linear_prec, cfg.turb_linear_tol,
-                                 cfg.turb_linear_iter, cfg.linear_restart, c->fs.turb_res.p, c->fs.turb_sol.p, &res);
+  c->lin_iters[1] = turb_linear_solve(c, &res);
   c->lin_res[1] = res;
   if (iterations) *iterations = c->lin_iters[1];
   if (residual) *residual = res;
@@ -300,8 +350,7 @@ int su2b200_iterate(su2b200_ctx* c, int nIter, su2b200_iter_report* reports) {
       const double trms = trms2[0];
       const auto& cfg = c->cfg;
       double res = 0.0;
-      c->lin_iters[1] = linsys_solve(c, c->sys[1], cfg.turb_linear_solver, cfg.turb_linear_prec, cfg.turb_linear_tol,
-                                     cfg.turb_linear_iter, cfg.linear_restart, s.turb_res.p, s.turb_sol.p, &res);
+      c->lin_iters[1] = turb_linear_solve(c, &res);
       c->lin_res[1] = res;
       turb_complete_implicit(c);
       turb_postprocessing(c);
