@@ -119,7 +119,7 @@ def slab_planes(n_planes, world):
     return [n_planes * r // world for r in range(world + 1)]
 
 
-def compare(parts, whole_gid, whole):
+def compare(parts, whole_gid, whole, single_precision=False):
     """parts: [(gid, out)] per rank.  Returns the summary dict that bench.py prints as `multigpu_parity`."""
     pos = {int(g): k for k, g in enumerate(whole_gid)}
     worst = 0.0
@@ -144,7 +144,10 @@ def compare(parts, whole_gid, whole):
     return {"max_rel": worst, "rms_rel": rms_rel, "iters_equal": iters_equal, "cl_rel": coef("CL"), "cd_rel": coef("CD"),
             "iters": [int(x) for x in p0["iters"]], "iters_one_gpu": [int(x) for x in whole["iters"]],
             "detail": detail, "steps": int(len(p0["iters"])),
-            "ok": bool(worst <= 1e-9 and rms_rel <= 1e-8 and iters_equal and coef("CL") <= 1e-6 and coef("CD") <= 1e-6)}
+            # mixed precision: the ranks' dot products are summed in another order than on one GPU, in single precision
+            "ok": bool(worst <= (1e-3 if single_precision else 1e-9) and rms_rel <= (1e-2 if single_precision else 1e-8)
+                       and (iters_equal or single_precision) and coef("CL") <= (1e-4 if single_precision else 1e-6)
+                       and coef("CD") <= (1e-4 if single_precision else 1e-6))}
 
 
 def whole_iteration_parity(cfg_text, n_planes, n_iter, rank, world, device, comm_id, gather, overrides=None,
@@ -159,4 +162,4 @@ def whole_iteration_parity(cfg_text, n_planes, n_iter, rank, world, device, comm
         return None
     gw, whole = run_iterations(cfg_text, n_iter, 0, 1, device, overrides=overrides, su2_path=su2_path, nparts=world,
                                partition_planes=None if su2_path else slab_planes(n_planes, world))
-    return compare(parts, gw, whole)
+    return compare(parts, gw, whole, single_precision=bool((overrides or {}).get("mixed_precision")))

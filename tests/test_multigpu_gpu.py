@@ -7,7 +7,7 @@ ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 
 @pytest.mark.gpu
 @pytest.mark.parametrize("kind", ["RANS", "NAVIER_STOKES", "EULER", "EULER_JST", "NAVIER_STOKES_JST",
-                                  "ITER_RANS", "ITER_EULER", "ITER_TET_EULER", "ITER_TET_RANS", "ITER_SST"])
+                                  "ITER_RANS", "ITER_EULER", "ITER_TET_EULER", "ITER_TET_RANS", "ITER_SST", "ITER_MIXED"])
 def test_two_slabs_match_the_undivided_mesh(kind):
     import torch
     if torch.cuda.device_count() < 2:

@@ -83,7 +83,8 @@ def whole_iterations(kind, rank, world, local):
             m.close()
         dist.barrier()
     sst = kind == "SST"
-    text = bench.make_cfg("RANS" if sst else kind, [12, 10, n_planes], 1)
+    mixed = kind == "MIXED"  # RANS-SA with the single-precision linear solve (float halo exchange, float allreduces)
+    text = bench.make_cfg("RANS" if (sst or mixed) else kind, [12, 10, n_planes], 1)
     if sst:
         text = text.replace("KIND_TURB_MODEL= SA", "KIND_TURB_MODEL= SST")
     if su2_path:
@@ -107,7 +108,8 @@ def whole_iterations(kind, rank, world, local):
         dist.all_gather_object(parts, obj)
         return parts
 
-    res = whole_iteration_parity(text, n_planes, 5, rank, world, local, comm, gather, su2_path=su2_path)
+    res = whole_iteration_parity(text, n_planes, 5, rank, world, local, comm, gather, su2_path=su2_path,
+                                 overrides={"mixed_precision": 1} if mixed else None)
     ok = 1.0
     if rank == 0:
         print("multigpu parity, whole iterations (%s, %d ranks): %s" % (kind, world, res))
