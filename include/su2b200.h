@@ -454,6 +454,10 @@ int su2b200_comm_init(su2b200_ctx* ctx, int rank, int size, const unsigned char 
  * Without it, or if _connect fails, the NCCL path stays in use. SU2B200_MAILBOX=0 disables it. */
 int su2b200_comm_mailbox_create(su2b200_ctx* ctx, unsigned char handle[64]);
 int su2b200_comm_mailbox_connect(su2b200_ctx* ctx, const unsigned char* handles /*[size][64]*/);
+/* The mailboxes are used only after EVERY rank has connected: the caller allgathers the return codes of _connect and
+ * calls _enable(ctx, all ranks succeeded) on every rank (a rank on NCCL and a rank on mailboxes would wait for each
+ * other forever). */
+int su2b200_comm_mailbox_enable(su2b200_ctx* ctx, int on);
 /* halo exchange of a named per-point array (MPI_QUANTITIES: SOLUTION, PRIMITIVE_GRADIENT, PRIMITIVE_LIMITER, ...):
  * InitiateComms + CompleteComms in one call; count per point = su2b200_array_size / nPoint; no-op on a single rank */
 int su2b200_halo_exchange(su2b200_ctx* ctx, int which_array);

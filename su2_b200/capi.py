@@ -112,7 +112,7 @@ EXPORTED_SYMBOLS = [
     "su2b200_vector_dot", "su2b200_vector_dot_noalloc", "su2b200_mg_link", "su2b200_mg_set_restricted_solution", "su2b200_mg_set_residual_term",
     "su2b200_mg_set_forcing_term", "su2b200_mg_get_prolongated_correction", "su2b200_mg_smooth_prolongated_correction",
     "su2b200_mg_set_prolongated_correction", "su2b200_mg_iterate", "su2b200_restart_write", "su2b200_restart_read",
-    "su2b200_restart_write_arrays", "su2b200_restart_read_arrays", "su2b200_comm_unique_id", "su2b200_comm_init", "su2b200_comm_mailbox_create", "su2b200_comm_mailbox_connect", "su2b200_halo_exchange",
+    "su2b200_restart_write_arrays", "su2b200_restart_read_arrays", "su2b200_comm_unique_id", "su2b200_comm_init", "su2b200_comm_mailbox_create", "su2b200_comm_mailbox_connect", "su2b200_comm_mailbox_enable", "su2b200_halo_exchange",
     "su2b200_timer_start", "su2b200_timer_stop", "su2b200_launch_count", "su2b200_bench_edge_kernel",
     "su2b200_bench_spmv", "su2b200_bench_prec", "su2b200_struct_sizes",
     "su2b200_mesh_create_box", "su2b200_mesh_read_su2", "su2b200_mesh_write_su2", "su2b200_mesh_stretch", "su2b200_mesh_partition", "su2b200_mesh_destroy", "su2b200_mesh_set_marker",

@@ -165,6 +165,7 @@ bool mailbox_view(su2b200_ctx* c, MailboxView* v) {
 
 void mailbox_release(su2b200_ctx* c) {
   c->mbox_ready = false;
+  c->mbox_connected = false;
   for (int r = 0; r < su2b200_ctx::MBOX_MAX_RANKS; ++r) {
     if (c->mbox_peer_host[r] && r != c->rank) cudaIpcCloseMemHandle(c->mbox_peer_host[r]);
     c->mbox_peer_host[r] = nullptr;
@@ -262,8 +263,15 @@ int su2b200_comm_mailbox_connect(su2b200_ctx* c, const unsigned char* handles) {
     }
     c->mbox_peers.upload(table);
     SU2B_CUDA(cudaDeviceSynchronize());
-    static const bool enabled = !(getenv("SU2B200_MAILBOX") && atoi(getenv("SU2B200_MAILBOX")) == 0);
-    c->mbox_ready = enabled;
+    c->mbox_connected = true;  // in use only after su2b200_comm_mailbox_enable: every rank must have got this far
+    return 0;
+  } catch (const std::exception& e) { set_error(e.what()); return 1; }
+}
+int su2b200_comm_mailbox_enable(su2b200_ctx* c, int on) {
+  try {
+    if (!c) throw Error("null context");
+    static const bool allowed = !(getenv("SU2B200_MAILBOX") && atoi(getenv("SU2B200_MAILBOX")) == 0);
+    c->mbox_ready = on != 0 && c->mbox_connected && allowed;
     return 0;
   } catch (const std::exception& e) { set_error(e.what()); return 1; }
 }

@@ -282,7 +282,8 @@ struct su2b200_ctx {
   unsigned long long* mbox_local = nullptr;          // device, cudaMalloc'ed (exported through cudaIpc)
   unsigned long long* mbox_peer_host[MBOX_MAX_RANKS] = {};
   su2b200::dvec<unsigned long long> mbox_peers;      // device table of the nranks mailbox addresses (own one included)
-  bool mbox_ready = false;
+  bool mbox_connected = false;  // peers' handles opened
+  bool mbox_ready = false;      // agreed by all ranks (su2b200_comm_mailbox_enable)
   // overlapped exchange (e3): pack on the compute stream, send/recv + unpack on comm_stream, joined by events
   cudaEvent_t ev_packed = nullptr, ev_unpacked = nullptr;
   bool exchange_in_flight = false;

@@ -154,10 +154,14 @@ class FlowSolver:
         """Peer-memory allreduce of the Krylov scalars (su2b200_comm_mailbox_*). `allgather(bytes) -> [bytes per rank]` is
         the caller's collective (torch.distributed, MPI...). Returns False (NCCL stays in use) if the handles cannot be opened."""
         h = (C.c_ubyte * 64)()
-        check(self.lib.su2b200_comm_mailbox_create(self.ctx, h))
-        allh = allgather(bytes(h))
-        buf = (C.c_ubyte * (64 * len(allh))).from_buffer_copy(b"".join(allh))
-        return self.lib.su2b200_comm_mailbox_connect(self.ctx, buf) == 0
+        ok = self.lib.su2b200_comm_mailbox_create(self.ctx, h) == 0
+        allh = allgather(bytes(h))  # collective: every rank takes part whatever its own outcome
+        if ok:
+            buf = (C.c_ubyte * (64 * len(allh))).from_buffer_copy(b"".join(allh))
+            ok = self.lib.su2b200_comm_mailbox_connect(self.ctx, buf) == 0
+        everyone = all(f == b"\x01" for f in allgather(b"\x01" if ok else b"\x00"))
+        self.lib.su2b200_comm_mailbox_enable(self.ctx, int(everyone))
+        return everyone
 
     def halo_exchange(self, name):
         """InitiateComms/CompleteComms of a named per-point array (su2b200_halo_exchange)."""
