@@ -6,6 +6,7 @@
 #include <cstring>
 #include <string>
 #include <vector>
+#include <algorithm>
 #include <stdexcept>
 #include "../../include/su2b200.h"
 
@@ -146,7 +147,20 @@ struct LinSysT {
   int sweep_mode = 2;                // apply: 2 data-polling sweeps (precond_poll.cu), 1 flag sweeps, 0 launch per level
   int build_mode = 2;                // factor: 2 single-launch polling factorisation (precond_factor.cu), 1 flag sweep,
                                      //         0 launch per level
-  int wide_sweep = 4096, wide_factor = 4096;  // level width from which the nVar-lanes-per-row kernels take over
+  // level width from which the nVar-lanes-per-row kernels take over; 0 = by pattern: 256 when no row has more than three
+  // entries on either side of the diagonal (hexahedra, quadrilaterals: 185^3 apply 2.80 -> 2.67 ms, build 6.41 -> 6.25 ms
+  // against 4096), else 4096 (rows in chunks: tetrahedral box 5.7 ms at 4096, 6.3 ms at 512)
+  int wide_sweep = 0, wide_factor = 0;
+  int auto_wide() const {
+    int longest = 0;
+    for (int i = 0; i < Pd; ++i) {
+      longest = std::max(longest, h_dia_ptr[i] - h_row_ptr[i]);
+      int up = 0;
+      for (int k = h_dia_ptr[i] + 1; k < h_row_ptr[i + 1]; ++k) up += h_col_ind[k] < Pd;
+      longest = std::max(longest, up);
+    }
+    return longest <= 3 ? 256 : 4096;
+  }
   int factor_rows_mode = 1;                   // 0 warp-per-row only, 1 hybrid, 2 rows kernel only (k_factor_rows)
   bool parts_explicit = false;                // h_parts given by su2b200_linsys_set_partition_rows
   // generation of the matrix values (bumped by every writer of A) and the one the ILU factors were built from: the
