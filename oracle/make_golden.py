@@ -65,6 +65,7 @@ HISTORIES = {
     "naca0012_roe_long": ("naca0012_roe", {}, 600, 1),
     "naca0012_jst_long": ("naca0012_jst", {}, 600, 1),
     "box_rans_sa_long": ("box_rans_sa", {}, 250, 1),
+    "box_rans_sst_long": ("box_rans_sst", {}, 250, 1),
     "box_rans_sa_t4": ("box_rans_sa", {"MESH_BOX_SIZE": "21,17,13", "LINEAR_SOLVER_ITER": "25"}, 12, 4),
     # the reference built with -Denable-mixedprec=true (oracle/build_ref_mixed.sh): single-precision Jacobian and Krylov solve
     "box_rans_sa_mixed": ("box_rans_sa", {"MESH_BOX_SIZE": "21,17,13"}, 20, 1, "SU2_CFD_mixed"),

@@ -280,7 +280,7 @@ def test_prec_partitions_follow_the_hybrid_parallel_reference():
 
 
 # ---- parity gates (ii) and (iii) of SURVEY 8(d): long histories and converged force coefficients -----------------
-@pytest.mark.parametrize("case", ["naca0012_roe_long", "naca0012_jst_long", "box_rans_sa_long"])
+@pytest.mark.parametrize("case", ["naca0012_roe_long", "naca0012_jst_long", "box_rans_sa_long", "box_rans_sst_long"])
 def test_long_history_and_converged_coefficients(case):
     """Gate (ii): the rms history follows the reference's curve (same slope, same order) over the whole run;
     gate (iii): the CONVERGED CL / CD agree to 1e-6 relative.  600 iterations on the C1 mesh take the density residual
@@ -307,9 +307,12 @@ def test_long_history_and_converged_coefficients(case):
     for col, key in ((6, "CL"), (7, "CD")):
         if abs(hist[-1, col]) > 1e-8:
             assert abs(reps[-1][key] - hist[-1, col]) <= 1e-6 * abs(hist[-1, col]), (key, reps[-1][key], hist[-1, col])
-    if gold["cfg_rans_sa"]:
+    if gold["cfg_rans_sa"] or int(gold.get("cfg_rans_sst", 0)):
         mt = np.array([r["rms_turb"] for r in reps])
         assert np.max(np.abs(np.log10(mt[1:]) - np.log10(hist[1:, 5]))) <= 0.02
+    if int(gold.get("cfg_rans_sst", 0)):
+        mo = np.array([r["rms_turb2"] for r in reps])
+        assert np.max(np.abs(np.log10(mo[1:]) - np.log10(hist[1:, 12]))) <= 0.02
 
 
 # ---- restart files ----------------------------------------------------------------------------------------
