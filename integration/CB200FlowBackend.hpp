@@ -15,7 +15,8 @@
 //       CompleteImplicitIteration)                                    -> su2b200_flow_*             [default mode]
 // Geometry, markers and configuration come from the reference's own CGeometry / CConfig objects; the solution lives in
 // the reference's CVariable between iterations (uploaded before, downloaded after every iteration), so output, forces,
-// the turbulence solver and convergence monitoring stay the reference's.
+// the turbulence solver (SA or SST: its eddy viscosity, and for SST its k, are uploaded every iteration) and convergence
+// monitoring stay the reference's.
 #pragma once
 #ifdef HAVE_SU2B200
 
@@ -92,8 +93,10 @@ class CB200FlowBackend {
     const unsigned long nPoint = geometry->GetnPoint();
     const unsigned short nVar = flow->GetnVar(), nDim = geometry->GetnDim();
     const bool rans = config->GetKind_Turb_Model() != TURB_MODEL::NONE;
-    if (!flowCtx) SetupFlow(geometry, flow, config);
-    /*--- state in: Solution (and the eddy viscosity of the reference's turbulence solver) ---*/
+    const bool sst = config->GetKind_Turb_Model() == TURB_MODEL::SST;
+    if (!flowCtx) SetupFlow(geometry, flow, rans ? solver_container[turbSol] : nullptr, config);
+    /*--- state in: Solution (and the eddy viscosity of the reference's turbulence solver; with SST also (k, omega):
+     *    k enters the static energy of the flow primitives, CNSVariable::SetPrimVar) ---*/
     std::vector<double> buf((size_t)nPoint * nVar);
     for (unsigned long i = 0; i < nPoint; ++i)
       for (unsigned short v = 0; v < nVar; ++v) buf[i * nVar + v] = SU2_TYPE::GetValue(flow->GetNodes()->GetSolution(i, v));
@@ -102,6 +105,12 @@ class CB200FlowBackend {
       std::vector<double> mut(nPoint);
       for (unsigned long i = 0; i < nPoint; ++i) mut[i] = SU2_TYPE::GetValue(solver_container[turbSol]->GetNodes()->GetmuT(i));
       B200_CHECK(su2b200_array_upload(flowCtx, SU2B200_ARR_EDDY_VISC, mut.data()));
+    }
+    if (sst) {
+      std::vector<double> kw((size_t)nPoint * 2);
+      for (unsigned long i = 0; i < nPoint; ++i)
+        for (unsigned short v = 0; v < 2; ++v) kw[i * 2 + v] = SU2_TYPE::GetValue(solver_container[turbSol]->GetNodes()->GetSolution(i, v));
+      B200_CHECK(su2b200_array_upload(flowCtx, SU2B200_ARR_TURB_SOLUTION, kw.data()));
     }
     /*--- CMultiGridIntegration::MultiGrid_Cycle at MGLEVEL 0 (CMultiGridIntegration.cpp:163-206), call by call ---*/
     unsigned long nonPhys = 0, iters = 0;
@@ -181,7 +190,7 @@ class CB200FlowBackend {
 
   /*--- geometry + markers + configuration of the flow problem, once (after CSolver construction) ---*/
   template <class Solver>
-  void SetupFlow(CGeometry* g, Solver* flow, CConfig* c) {
+  void SetupFlow(CGeometry* g, Solver* flow, Solver* turb, CConfig* c) {
     B200_CHECK(su2b200_create(Device(), &flowCtx));
     const unsigned long nDim = g->GetnDim(), P = g->GetnPoint(), Pd = g->GetnPointDomain(), E = g->GetnEdge();
     std::vector<unsigned long> e0(E), e1(E);
@@ -281,6 +290,15 @@ class CB200FlowBackend {
       const double mu = val(c->GetViscosity_FreeStreamND());
       const double chi = f.nu_tilde_inf / (mu / f.density_inf);
       f.eddy_visc_inf = f.density_inf * chi * chi * chi / (chi * chi * chi + 7.1 * 7.1 * 7.1) * f.nu_tilde_inf;
+    }
+    if (turb && c->GetKind_Turb_Model() == TURB_MODEL::SST) {
+      /*--- free stream of the CTurbSSTSolver constructor (CTurbSSTSolver.cpp:118-147); energy_inf above already holds k
+       *    (CEulerSolver::SetNondimensionalization adds Tke_FreeStreamND when the model needs it) ---*/
+      f.rans_sst = 1;
+      f.kine_inf = val(turb->GetTke_Inf()); f.omega_inf = val(turb->GetOmega_Inf());
+      f.eddy_visc_inf = f.density_inf * f.kine_inf / f.omega_inf;
+      f.sst_lower[0] = 1.0e-10; f.sst_lower[1] = 1.0e-4; f.sst_upper[0] = 1.0e10; f.sst_upper[1] = 1.0e15;
+      f.max_update_sst = val(c->GetMaxUpdateFractionSST());
     }
     B200_CHECK(su2b200_flow_configure(flowCtx, &f));
     B200_CHECK(su2b200_flow_allocate(flowCtx));

@@ -4,7 +4,7 @@ scratch copy of the reference by integration/build_shim.sh) and run with ENABLE_
 the history of the unmodified reference (tests/golden/*.npz): rms residuals and CL/CD to 1e-6 relative, equal Krylov
 iteration counts.  Geometry and configuration reach the library from the reference's objects, not from mesh_host.cu /
 config.py.  Two modes: the whole implicit iteration on the device (default) and only System.Solve (SU2B200_MODE=linear).
-The RANS case keeps the reference's CPU turbulence solver, whose Krylov solver then multiplies through the patched
+The RANS cases (SA and SST) keep the reference's CPU turbulence solver, whose Krylov solver then multiplies through the patched
 CSysMatrixVectorProduct::operator() (the reference's own GPU hook) -> su2b200_linsys_spmv."""
 import os
 import re
@@ -59,7 +59,7 @@ def _run(case, n_iter, mode):
 
 
 @pytest.mark.parametrize("mode", ["iteration", "linear"])
-@pytest.mark.parametrize("case", ["box_euler", "rect_ns", "box_rans_sa"])
+@pytest.mark.parametrize("case", ["box_euler", "rect_ns", "box_rans_sa", "box_rans_sst"])
 def test_reference_driver_with_the_binding_reproduces_the_reference_history(case, mode):
     if not os.path.exists(EXE):
         pytest.skip("integration/_ref/SU2_CFD_b200 not built (integration/build_shim.sh, needs /root/reference)")
@@ -70,8 +70,13 @@ def test_reference_driver_with_the_binding_reproduces_the_reference_history(case
     assert len(rows) == n
     nd = int(gold["nDim"])
     keys = ["rms[Rho]", "rms[RhoU]", "rms[RhoV]"] + (["rms[RhoW]"] if nd == 3 else []) + ["rms[RhoE]"]
+    sst = "cfg_rans_sst" in gold and bool(gold["cfg_rans_sst"])
     for i, r in enumerate(rows):
         ref = hist[i, :nd + 2]
+        if sst:  # the reference's own CTurbSSTSolver, fed by the device flow state: (k, omega) residuals and Krylov count
+            assert abs(10.0 ** r["rms[k]"] - hist[i, 5]) <= 1e-6 * abs(hist[i, 5]), (i, r["rms[k]"], hist[i, 5])
+            assert abs(10.0 ** r["rms[w]"] - hist[i, 12]) <= 1e-6 * abs(hist[i, 12]), (i, r["rms[w]"], hist[i, 12])
+            assert int(r["LinSolIterTurb"]) == int(hist[i, 10])
         if np.max(np.abs(ref)) < 1e-14:
             continue  # uniform free stream: round-off residual in both codes
         got = np.array([10.0 ** r[k] for k in keys])
