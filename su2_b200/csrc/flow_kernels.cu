@@ -648,34 +648,31 @@ __global__ void k_prepare_implicit(int Pd, const int* __restrict__ dia_ptr, cons
 template <int NV>
 __global__ void k_residual_final(int nb, const double* __restrict__ part_rms, const double* __restrict__ part_max,
                                  const int* __restrict__ part_idx, double* __restrict__ out /*[3*NV]*/) {
-  // single block of 256 threads: thread t reduces a contiguous chunk of the block partials in order, thread 0 then
-  // combines the chunks in ascending order (fixed summation order whatever the launch; first maximum wins)
+  // one block of 256 threads per variable: thread t reduces a contiguous chunk of the block partials in order, thread 0
+  // then combines the chunks in ascending order (fixed summation order whatever the launch; first maximum wins)
   __shared__ double sa[256], sm[256];
   __shared__ int si[256];
-  const int t = threadIdx.x;
+  const int t = threadIdx.x, v = blockIdx.x;
   const int per = (nb + 255) / 256;
   const int b0 = min(t * per, nb), b1 = min(b0 + per, nb);
-  for (int v = 0; v < NV; ++v) {
-    double a = 0.0, m = 0.0;
-    int id = 0;
-    for (int b = b0; b < b1; ++b) {
-      a += part_rms[(size_t)b * NV + v];
-      const double mb = part_max[(size_t)b * NV + v];
-      if (mb > m) { m = mb; id = part_idx[(size_t)b * NV + v]; }
+  double a = 0.0, m = 0.0;
+  int id = 0;
+  for (int b = b0; b < b1; ++b) {
+    a += part_rms[(size_t)b * NV + v];
+    const double mb = part_max[(size_t)b * NV + v];
+    if (mb > m) { m = mb; id = part_idx[(size_t)b * NV + v]; }
+  }
+  sa[t] = a; sm[t] = m; si[t] = id;
+  __syncthreads();
+  if (t == 0) {
+    a = 0.0; m = 0.0; id = 0;
+    for (int k = 0; k < 256; ++k) {
+      a += sa[k];
+      if (sm[k] > m) { m = sm[k]; id = si[k]; }
     }
-    sa[t] = a; sm[t] = m; si[t] = id;
-    __syncthreads();
-    if (t == 0) {
-      a = 0.0; m = 0.0; id = 0;
-      for (int k = 0; k < 256; ++k) {
-        a += sa[k];
-        if (sm[k] > m) { m = sm[k]; id = si[k]; }
-      }
-      out[v] = a;
-      out[NV + v] = m;
-      out[2 * NV + v] = (double)id;
-    }
-    __syncthreads();
+    out[v] = a;
+    out[NV + v] = m;
+    out[2 * NV + v] = (double)id;
   }
 }
 
@@ -1094,7 +1091,7 @@ static void prepare_implicit_impl(su2b200_ctx* c, LinSys& ls, const double* dt, 
   double* out = s.red.p + (size_t)3 * nb * NV;
   LAUNCH(c, k_prepare_implicit<NV>, nb, 256, g.Pd, ls.dia_ptr, g.volume.p, dt, ls.A.p, res, trunc, sol, part_rms,
          part_max, part_idx);
-  LAUNCH(c, k_residual_final<NV>, 1, 256, nb, part_rms, part_max, part_idx, out);
+  LAUNCH(c, k_residual_final<NV>, NV, 256, nb, part_rms, part_max, part_idx, out);
   const size_t b = (size_t)g.Pd * NV, e = (size_t)g.P * NV;
   if (e > b) LAUNCH(c, k_zero_range, nblk(e - b, 256), 256, res, sol, b, e);
   SU2B_CUDA(cudaMemcpyAsync(s.h_red, out, 3 * NV * sizeof(double), cudaMemcpyDeviceToHost, c->stream));
