@@ -368,3 +368,37 @@ def test_unstructured_partition_of_the_quickstart_mesh(nranks):
         return m
 
     _partition_checks(make, nranks)
+
+
+def test_shim_patch_anchors_match_the_reference(tmp_path):
+    """integration/apply_patch.py on a scratch copy of the five reference files it edits: every anchor must be found
+    exactly once (the script stops otherwise), the edits must sit behind HAVE_SU2B200, and a second run must be a no-op.
+    Needs the reference tree (this container); the GPU box only uses the prebuilt integration/_ref/SU2_CFD_b200."""
+    ref = os.environ.get("SU2_REFERENCE", "/root/reference")
+    files = ["Common/include/linear_algebra/CSysMatrix.hpp", "Common/include/linear_algebra/CMatrixVectorProduct.hpp",
+             "SU2_CFD/include/solvers/CSolver.hpp", "SU2_CFD/include/solvers/CFVMFlowSolverBase.inl",
+             "SU2_CFD/src/integration/CMultiGridIntegration.cpp"]
+    if not all(os.path.exists(os.path.join(ref, f)) for f in files):
+        pytest.skip("no reference tree at %s" % ref)
+    import importlib.util
+    import shutil
+    for f in files:
+        dst = tmp_path / f
+        dst.parent.mkdir(parents=True, exist_ok=True)
+        shutil.copy(os.path.join(ref, f), dst)
+        os.chmod(dst, 0o644)
+    spec = importlib.util.spec_from_file_location("apply_patch", os.path.join(ROOT, "integration", "apply_patch.py"))
+    mod = importlib.util.module_from_spec(spec)
+    spec.loader.exec_module(mod)
+    mod.main(str(tmp_path), ROOT)
+    patched = {f: (tmp_path / f).read_text() for f in files}
+    for f, text in patched.items():
+        assert "HAVE_SU2B200" in text, f
+        assert text.count("#ifdef HAVE_SU2B200") + text.count("#if defined(HAVE_SU2B200)") >= 1, f
+        orig = open(os.path.join(ref, f)).read()
+        assert len(text) > len(orig)  # additions only; every one of them sits behind the macro
+    assert (tmp_path / "Common/include/linear_algebra/CB200FlowBackend.hpp").exists()
+    assert (tmp_path / "Common/include/linear_algebra/su2b200.h").exists()
+    mod.main(str(tmp_path), ROOT)  # idempotent
+    for f in files:
+        assert (tmp_path / f).read_text() == patched[f], f
